@@ -1,0 +1,212 @@
+/* cf_abi.h - C ABI of the B200 batched CrazyFlie hover environment and fused GAE.
+ *
+ * The reference (Hu-Hanyang/disturbance-CrazyFile-simulation) is pure Python and has
+ * no FFI; the interface this library sits behind is the gym `Env` made by
+ * `gym.make(id)` and its `reset()` / `step(action)` (envs/base.py:420-507 and the
+ * step overrides envs/hover_free.py:391-444, 608-665, 778-833, envs/hover.py:649-705,
+ * 866-926, 1036-1094, 1388-1444), plus `Buffer.finish_path` for GAE
+ * (algs/core.py:498-535).  Each entry point below cites what it replaces.  The Python
+ * binding a maintainer would add (ctypes) is shown in INTEGRATION.md.
+ *
+ * Conventions: every call returns 0 on success or a negative cf_status; no C++
+ * exception crosses the boundary; `cf_last_error()` gives the message of the last
+ * failure on the calling thread.  All env-major buffers (`act`, `obs`, `rew`, ...)
+ * are caller-owned and contiguous.  The `_dev` entry points take DEVICE pointers and
+ * are asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy default
+ * stream).  The `_host` entry points take HOST pointers, do the host<->device copies
+ * themselves and return when the results are in the host buffers.
+ * One handle <-> one device <-> one stream at a time; distinct handles are independent.
+ */
+#ifndef CF_ABI_H
+#define CF_ABI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CF_ABI_VERSION 1
+
+typedef enum cf_status {
+    CF_OK = 0,
+    CF_ERR_INVALID = -1,   /* bad argument / unsupported configuration */
+    CF_ERR_CUDA = -2,      /* CUDA runtime error (message in cf_last_error) */
+    CF_ERR_NO_TABLE = -3,  /* an HJ disturbance level has no value table loaded */
+    CF_ERR_ALLOC = -4
+} cf_status;
+
+/* disturbance source of the env variant (the classes differ only in this) */
+enum {
+    CF_DSTB_NONE = 0,          /* *WithoutAdversary: dstb = (0,0,0)   hover_free.py:814 */
+    CF_DSTB_HJ_FIXED = 1,      /* *WithAdversary[Initial]: fixed level  hover_free.py:319,425 */
+    CF_DSTB_HJ_BOLTZMANN = 2,  /* *WithRandomHJAdversary: Boltzmann() at the end of reset, hover_free.py:536 */
+    CF_DSTB_RANDOM_BOX = 3     /* *WithRandomAdversary: dstb_space.sample(), hover_free.py:878,986 */
+};
+
+enum { CF_REWARD_FREE = 0,    /* envs/hover_free.py:206-235 */
+       CF_REWARD_TARGET = 1   /* envs/hover.py:184-202 (-|xyz - target|) */ };
+
+/* noise source */
+enum { CF_RNG_PHILOX = 0,     /* counter-based Philox4x32-10 keyed by (seed, global env id) */
+       CF_RNG_INJECTED = 1    /* parity mode: standard draws supplied by cf_set_noise_override */ };
+
+enum { CF_HJ_VALUE_TABLE = 0, /* gather 5 fp32 values of V per env-step (distur_gener.py:40-99) */
+       CF_HJ_SIGN_TABLE = 1   /* 2-bit/cell sign table precomputed on load with the same fp32 rule */ };
+
+#define CF_ACT_DIM 4
+#define CF_OBS13 13
+#define CF_HJ_PTS 15
+#define CF_HJ_CELLS 11390625      /* 15^6 */
+#define CF_MAX_LEVELS 31          /* level index = round(level*10), levels <= 3.0 (distur_gener.py:154) */
+
+/* live standard draws consumed per env-step / per reset */
+#define CF_STEP_NORMALS 44
+#define CF_STEP_UNIFORMS 8        /* 6 sensor-noise + 2 random-box disturbance */
+#define CF_RESET_NORMALS 48
+#define CF_RESET_UNIFORMS 42
+
+/* Constructor kwargs of the reference env classes, flattened.  Defaults are filled by
+ * cf_config_default(); cites in cf_abi.cu. */
+typedef struct cf_config {
+    int32_t abi_version;             /* CF_ABI_VERSION */
+    int32_t reward_kind;             /* CF_REWARD_* */
+    int32_t disturbance_kind;        /* CF_DSTB_* */
+    int32_t observation_noise;       /* >0: SensorNoise pipeline, obs 34-d; <=0: exact state, obs 42-d */
+    int32_t enable_reset_distribution;
+    int32_t aggregate_phy_steps;     /* physics substeps per control step (2) */
+    int32_t max_episode_steps;       /* gym TimeLimit (500); <=0 disables */
+    int32_t gyroscopic;              /* Bullet model switch B2 */
+    int32_t use_ground_effect;       /* physics.py:18,25 (reference never enables it) */
+    int32_t hj_mode;                 /* CF_HJ_* */
+    int32_t rng_mode;                /* CF_RNG_* */
+    int32_t auto_reset;              /* 1: done envs are reset inside cf_step */
+    double domain_randomization;     /* <=0 off; 0.1 = +-10 % */
+    double disturbance_level;        /* CF_DSTB_HJ_FIXED */
+    double penalty_action, penalty_angle, penalty_spin, penalty_terminal, penalty_velocity, penalty_z;
+    double done_roll_pitch_rad;      /* deg2rad(75) (60 for the base classes) */
+    double done_rate_deg;            /* 1000 (300) deg/s, compared as rad2deg(|w|) > limit */
+    double init_pos_lim, init_angle, init_yaw, init_vel_lim, init_rate_lim, init_yaw_rate_lim;
+    double cost_rate_limit;          /* rpy_dot_limit, deg2rad(200) (Initial variant: deg2rad(300)) */
+    double sim_time_step;            /* 1/200 */
+    double motor_time_constant;      /* 0.080 */
+    double motor_thrust_noise;       /* 0.05 -> OU sigma 0.2*0.05 */
+    double latency;                  /* 0.015 -> ring of int(latency // time_step) = 2 */
+    double linear_damping, angular_damping;   /* Bullet model switch B3 (0.04) */
+} cf_config;
+
+typedef struct cf_env cf_env;
+
+/* Host-visible state record: CF_STATE_WORDS 32-bit words per env, env-major
+ * ([n_envs][CF_STATE_WORDS]); words are float unless marked (i) = int32/uint32 bits. */
+enum {
+    CF_S_POS = 0,        /* 3 */
+    CF_S_EP_RET = 3,     /* 1  running episode return */
+    CF_S_QUAT = 4,       /* 4  [x,y,z,w] */
+    CF_S_VEL = 8,        /* 3  world */
+    CF_S_OMEGA_W = 11,   /* 3  world-frame angular velocity (as Bullet stores it) */
+    CF_S_LPF = 14,       /* 3  gyro low-pass state */
+    CF_S_GYRO_BIAS = 17, /* 3 */
+    CF_S_MOTOR_X = 20,   /* 4  PT1 motor state */
+    CF_S_OU = 24,        /* 4  thrust-noise OU state */
+    CF_S_RING = 28,      /* 8  action latency ring [2][4] */
+    CF_S_ACT_PREV1 = 36, /* 4  u(k-1) */
+    CF_S_ACT_PREV2 = 40, /* 4  u(k-2) */
+    CF_S_OBS_PREV = 44,  /* 13 last emitted obs13 */
+    CF_S_EP_LEN = 57,    /* (i) steps since reset */
+    CF_S_RNG_CTR = 58,   /* (i) per-env RNG event counter */
+    CF_S_MISC = 59,      /* (i) level_idx | ring_idx<<8 | iteration<<12 | fresh<<31 */
+    CF_S_DT = 60,        /* domain-randomised parameters: 14 words */
+    CF_S_MASS = 61,
+    CF_S_INERTIA = 62,   /* 3 */
+    CF_S_FTF1 = 65,
+    CF_S_MOTOR_B = 66,   /* 4  T_s/T  (A = 1 - B) */
+    CF_S_MOTOR_K = 70,   /* 4 */
+    CF_STATE_WORDS = 76
+};
+
+/* ---- lifecycle -------------------------------------------------------------------- */
+/* Fill `cfg` with the constructor defaults of a registered env id, e.g.
+ * "DroneHoverBulletFreeEnvWithRandomHJAdversary-v0" (phoenix_drone_simulation/__init__.py:8-109). */
+int cf_config_default(const char* env_id, cf_config* cfg);
+
+/* gym.make(id, **kwargs) for n_envs envs whose global ids are env_id_base..env_id_base+n_envs-1
+ * (RNG is keyed by the global id, so results do not depend on how envs are sharded over GPUs). */
+int cf_create(const cf_config* cfg, int32_t n_envs, int32_t device, uint64_t seed,
+              int64_t env_id_base, cf_env** out);
+int cf_destroy(cf_env* env);
+int cf_obs_dim(const cf_env* env);       /* 34 (noise on) or 42 (noise off), envs/base.py:139-141 */
+int cf_num_envs(const cf_env* env);
+
+/* np.load(fastrack_{level}_15x15.npy) of distur_gener.py:155, hoisted: upload one float32
+ * (15,)*6 C-order value table (HOST pointer) for level index round(level*10). */
+int cf_load_hj_table(cf_env* env, int32_t level_idx, const float* V_host);
+/* read back the packed 2-bit sign table of a level (HOST pointer, CF_HJ_CELLS/4+1 bytes) */
+int cf_get_hj_signs(cf_env* env, int32_t level_idx, uint8_t* out_host);
+
+/* ---- device-pointer API (asynchronous on `stream`) ---------------------------------- */
+/* env.reset() (envs/base.py:420-464; hover_free.py:492-538) for envs with mask[i]!=0 (mask NULL = all).
+ * obs: [n_envs][obs_dim] float32 (rows of unmasked envs untouched). */
+int cf_reset_dev(cf_env* env, const uint8_t* mask, float* obs, void* stream);
+
+/* env.step(action) under TimeLimit for all envs.  act [n][4]; obs [n][obs_dim]; rew [n];
+ * done [n] (1 = terminal or time-limit); cost [n] (info['cost'], may be NULL);
+ * term_obs [n][obs_dim] (observation before the auto-reset, written for done envs only; may be NULL);
+ * truncated [n] (info['TimeLimit.truncated'], may be NULL). */
+int cf_step_dev(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
+                float* cost, float* term_obs, uint8_t* truncated, void* stream);
+
+/* k env.step calls in one launch, state kept in registers: act [k][n][4], obs [k][n][obs_dim],
+ * rew/done/cost [k][n] (cost may be NULL). */
+int cf_step_k_dev(cf_env* env, int32_t k, const float* act, float* obs, float* rew,
+                  uint8_t* done, float* cost, void* stream);
+
+/* ---- host-pointer API (what a gym-style caller with NumPy buffers uses) -------------- */
+int cf_reset_host(cf_env* env, const uint8_t* mask, float* obs);
+int cf_step_host(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
+                 float* cost, float* term_obs, uint8_t* truncated);
+
+/* ---- state / parity hooks ----------------------------------------------------------- */
+int cf_get_state(cf_env* env, float* state_host /* [n][CF_STATE_WORDS] */);
+int cf_set_state(cf_env* env, const float* state_host);
+/* disturbance_level of each env (info['disturbance_level']) */
+int cf_get_levels(cf_env* env, float* levels_host);
+/* parity mode (rng_mode = CF_RNG_INJECTED): standard normal / U[0,1) draws for the NEXT call.
+ * step:  normals [CF_STEP_NORMALS][n],  uniforms [CF_STEP_UNIFORMS][n]
+ * reset: normals [CF_RESET_NORMALS][n], uniforms [CF_RESET_UNIFORMS][n]  (slot-major, HOST pointers;
+ * either may be NULL to leave that set unchanged).  Layout of the slots: DESIGN.md "noise slots". */
+int cf_set_noise_override(cf_env* env, const float* step_normals, const float* step_uniforms,
+                          const float* reset_normals, const float* reset_uniforms);
+/* grid indices and disturbance of the HJ lookup for given (roll,pitch,yaw,p,q,r) states
+ * (Grid.get_index + spa_deriv + opt_dstb_non_hcl, distur_gener.py:40-125); states [n][6] float64,
+ * idx [n][6] int32, dstb [n][2] float32 sign codes (+1/-1); HOST pointers. */
+int cf_hj_lookup_host(cf_env* env, int32_t level_idx, const double* states, int32_t n,
+                      int32_t* idx, float* dstb_sign);
+
+/* ---- PPO GAE (Buffer.finish_path, algs/core.py:498-535; discount_cumsum :105-119) ----- */
+/* Time-major rollout [T][N].  A path ends after step t of env n when done[t][n] != 0; its
+ * bootstrap value is end_val[t][n] (0 for a true terminal, V(s_T) for a time-limit cut,
+ * iwpg.py:392-402); paths still open at t = T-1 bootstrap from last_val[n].
+ * rew_scale: reward divisor 1/(ret_std+1e-5) applied with clip +-10 when > 0
+ * (use_scaled_rewards, online_mean_std.py:32-48); <= 0 disables scaling.
+ * Outputs adv, target_v, disc_ret [T][N].  DEVICE pointers, asynchronous on `stream`. */
+int cf_gae_dev(const float* rew, const float* val, const uint8_t* done, const float* end_val,
+               const float* last_val, float gamma, float lam, float rew_scale,
+               int32_t T, int32_t N, float* adv, float* target_v, float* disc_ret, void* stream);
+int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const float* end_val,
+                const float* last_val, float gamma, float lam, float rew_scale,
+                int32_t T, int32_t N, float* adv, float* target_v, float* disc_ret);
+
+/* number of kernels this library has launched on this handle since creation */
+int64_t cf_launch_count(const cf_env* env);
+/* average device time (ms) of the step kernel launches since the last call with reset!=0,
+ * measured with CUDA events on the launching stream when profiling was enabled */
+int cf_kernel_timing(cf_env* env, int32_t enable, int32_t reset, double* avg_ms, int64_t* launches);
+
+const char* cf_last_error(void);
+int cf_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CF_ABI_H */
