@@ -1,0 +1,563 @@
+// cf_abi.cu - host side of the C ABI declared in include/cf_abi.h: handle management, config
+// defaults of the registered env ids, HJ table upload, launch wrappers and the host-pointer API.
+// No C++ exception crosses the boundary; every entry point returns a cf_status.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "cf_kernels.h"
+
+using namespace cf;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, const char* a = "", long long b = 0) {
+    snprintf(g_err, sizeof(g_err), fmt, a, b);
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* where) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+    return CF_ERR_CUDA;
+}
+#define CU(call)                                                  \
+    do {                                                          \
+        cudaError_t e_ = (call);                                  \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);       \
+    } while (0)
+
+constexpr double kPiD = 3.141592653589793;
+double deg2rad(double x) { return kPiD * x / 180.0; }
+
+struct EventPair { cudaEvent_t a, b; };
+
+}  // namespace
+
+struct cf_env {
+    cf_config cfg;
+    DevCfg dev;
+    DevTables tab;
+    int n = 0, device = 0, obs_dim = 34;
+    float4* S = nullptr;
+    float* value_dev[CF_MAX_LEVELS] = {};
+    uint8_t* signs_dev[CF_MAX_LEVELS] = {};
+    float* inj[4] = {};              // step z, step u, reset z, reset u
+    float* fin_ret = nullptr;
+    int* fin_len = nullptr;
+    double* agg = nullptr;
+    float4* rec_dev = nullptr;       // scratch for get/set_state
+    // host-pointer API: private stream + device mirrors of the caller's host buffers
+    cudaStream_t hstream = nullptr;
+    float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_cost = nullptr, *d_term = nullptr;
+    uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
+    long long launches = 0;
+    bool timing = false;
+    std::vector<EventPair> ev_pool;
+    size_t ev_used = 0;
+    double ev_ms = 0.0;
+    long long ev_count = 0;
+};
+
+namespace {
+
+struct IdDefaults {
+    const char* id;
+    int reward, dstb;
+    double level, rp_deg, rate_deg, init_angle, cost_rate_deg;
+};
+// phoenix_drone_simulation/__init__.py:8-109 (registered ids) and the constructors / compute_done
+// overrides of envs/hover_free.py and envs/hover.py.  level: the class's hard-coded
+// disturbance_level (hover_free.py:319 -> 1.5; hover.py:577 -> 0.0; hover.py:1311 -> 1.5).
+const IdDefaults kIds[] = {
+    {"DroneHoverBulletFreeEnvWithoutAdversary-v0", CF_REWARD_FREE, CF_DSTB_NONE, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletFreeEnvWithAdversary-v0", CF_REWARD_FREE, CF_DSTB_HJ_FIXED, 1.5, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletFreeEnvWithRandomHJAdversary-v0", CF_REWARD_FREE, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnv-v0", CF_REWARD_TARGET, CF_DSTB_NONE, 0.0, 60, 300, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithoutAdversary-v0", CF_REWARD_TARGET, CF_DSTB_NONE, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_FIXED, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithRandomHJAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithCurriculumHJAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithRandomAdversary-v0", CF_REWARD_TARGET, CF_DSTB_RANDOM_BOX, 0.0, 75, 1000, kPiD / 6, 200},
+    {"DroneHoverBulletEnvWithAdversaryInitial-v0", CF_REWARD_TARGET, CF_DSTB_HJ_FIXED, 1.5, 75, 1000, kPiD / 4, 300},
+};
+
+void grid_tables(double grid[6][CF_HJ_PTS], double dx[6], double cdf[21]) {
+    // odp/Grid/GridProcessing.py:6-51 with the arguments of distur_gener.py:179; np.linspace:
+    // step = (hi-lo)/14, y_i = lo + i*step, last point forced to hi
+    for (int d = 0; d < 6; ++d) {
+        double lo = d < 3 ? -kPiD / 2.4 : -kPiD, hi = d < 3 ? kPiD / 2.4 : kPiD;
+        if (d < 3) hi = lo + (hi - lo) * (1.0 - 1.0 / 15.0);
+        dx[d] = (hi - lo) / (15.0 - 1.0);
+        double step = (hi - lo) / 14.0;
+        for (int i = 0; i < 15; ++i) grid[d][i] = lo + (double)i * step;
+        grid[d][14] = hi;
+    }
+    // Boltzmann() (envs/utils.py:27-39) through legacy np.random.choice(p=): p = w/np.sum(w)
+    // (pairwise 8-way unrolled sum for n < 128), cdf = cumsum(p), cdf /= cdf[-1]
+    double w[21], s, c = 0.0, r[8];
+    for (int i = 0; i < 21; ++i) w[i] = exp(-1.0 * (0.0 + (double)i * 0.1));
+    for (int j = 0; j < 8; ++j) r[j] = w[j];
+    int i = 8;
+    for (; i < 21 - (21 % 8); i += 8)
+        for (int j = 0; j < 8; ++j) r[j] += w[i + j];
+    s = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+    for (; i < 21; ++i) s += w[i];
+    for (int k = 0; k < 21; ++k) { c += w[k] / s; cdf[k] = c; }
+    double last = cdf[20];
+    for (int k = 0; k < 21; ++k) cdf[k] /= last;
+}
+
+int derive(const cf_config& c, uint64_t seed, int64_t gid_base, DevCfg& d) {
+    if (c.abi_version != CF_ABI_VERSION) return fail(CF_ERR_INVALID, "cf_config.abi_version mismatch%s (got %lld)", "", c.abi_version);
+    if (c.aggregate_phy_steps != 2) return fail(CF_ERR_INVALID, "aggregate_phy_steps must be 2%s (got %lld)", "", c.aggregate_phy_steps);
+    if (fabs(c.sim_time_step - 0.005) > 1e-12) return fail(CF_ERR_INVALID, "sim_time_step must be 1/200%s", "");
+    // action ring of int(latency // time_step) slots (agents.py:170-175); the kernel holds exactly 2
+    {   // Python float floor division
+        double mod = fmod(c.latency, c.sim_time_step), div = (c.latency - mod) / c.sim_time_step, fl = floor(div);
+        if (div - fl > 0.5) fl += 1.0;
+        if (c.latency < c.sim_time_step || (int)fl != 2)
+            return fail(CF_ERR_INVALID, "latency must give an action ring of 2 slots (0.010 <= latency < 0.015+)%s", "");
+    }
+    if (c.reward_kind != CF_REWARD_FREE && c.reward_kind != CF_REWARD_TARGET) return fail(CF_ERR_INVALID, "bad reward_kind%s", "");
+    if (c.disturbance_kind < CF_DSTB_NONE || c.disturbance_kind > CF_DSTB_RANDOM_BOX) return fail(CF_ERR_INVALID, "bad disturbance_kind%s", "");
+    int li = (int)lround(c.disturbance_level * 10.0);
+    if (c.disturbance_level < 0 || fabs(li / 10.0 - c.disturbance_level) > 1e-9)
+        return fail(CF_ERR_INVALID, "disturbance_level must be a non-negative multiple of 0.1%s", "");
+    if (li > 30) return fail(CF_ERR_INVALID, "disturbance_level must be <= 3.0 (distur_gener.py:154)%s", "");
+    memset(&d, 0, sizeof(d));
+    d.reward_kind = c.reward_kind; d.dstb_kind = c.disturbance_kind;
+    d.obs_noise = c.observation_noise > 0; d.reset_dist = c.enable_reset_distribution != 0;
+    d.agg_steps = 2; d.max_ep_steps = c.max_episode_steps;
+    d.gyroscopic = c.gyroscopic != 0; d.ground_effect = c.use_ground_effect != 0;
+    d.hj_mode = c.hj_mode; d.auto_reset = c.auto_reset != 0;
+    d.dr_on = c.domain_randomization > 0; d.injected = c.rng_mode == CF_RNG_INJECTED;
+    d.fixed_level_idx = c.disturbance_kind == CF_DSTB_HJ_FIXED ? li : 0;
+    d.obs_dim = d.obs_noise ? 34 : 42;
+    d.dr = (float)c.domain_randomization;
+    d.pen_action = (float)c.penalty_action; d.pen_angle = (float)c.penalty_angle; d.pen_spin = (float)c.penalty_spin;
+    d.pen_terminal = (float)c.penalty_terminal; d.pen_velocity = (float)c.penalty_velocity; d.pen_z = (float)c.penalty_z;
+    d.done_rp_rad = (float)c.done_roll_pitch_rad; d.done_rate_deg = (float)c.done_rate_deg;
+    d.init_pos = (float)c.init_pos_lim; d.init_angle = (float)c.init_angle; d.init_yaw = (float)c.init_yaw;
+    d.init_vel = (float)c.init_vel_lim; d.init_rate = (float)c.init_rate_lim; d.init_yaw_rate = (float)c.init_yaw_rate_lim;
+    d.cost_rate_limit = (float)c.cost_rate_limit;
+    d.sim_dt = (float)c.sim_time_step; d.motor_tc = (float)c.motor_time_constant;
+    d.ou_sigma = (float)(0.2 * c.motor_thrust_noise);         // agents.py:206
+    d.lin_damp = (float)c.linear_damping; d.ang_damp = (float)c.angular_damping;
+    const double M = 0.030, G = 9.81, T2W = 1.8;                // cf21x_bullet.urdf:12,21
+    d.nomA = (float)(1.0 - c.sim_time_step / c.motor_time_constant);
+    d.nomB = (float)(c.sim_time_step / c.motor_time_constant);
+    d.nomK = (float)((G * M) * T2W / 4.0);
+    d.hover_x = (float)sqrt(1.0 / T2W); d.hover_a = (float)(2.0 * 1.0 / T2W - 1.0);
+    // SensorNoise.add_noise_to_omega constants at dt = 1/SIM_FREQ (sensors.py:121-134, defaults :26-30)
+    const double dt = 1.0 / 200.0, dens = 0.000175, corr = 1000.0;
+    double sg = dens / pow(dt, 0.5);
+    d.gyro_sb = (float)pow(-(sg * sg) * (corr / 2.0) * (exp(-2.0 * dt / corr) - 1.0), 0.5);
+    d.gyro_pi = (float)exp(-dt / corr);
+    d.gyro_rw = 0.0105f; d.gyro_ton = (float)deg2rad(5.0);
+    d.quat_std = (float)deg2rad(0.1); d.quat_unif = (float)deg2rad(0.05);
+    {   // calculate_ground_effect, physics.py:27-58
+        const double kf = 3.16e-10, gnd = 11.36859, pr = 2.31348e-2;
+        double max_thrust = (G * M) * T2W / 4.0, max_rpm = sqrt((T2W * (G * M)) / (4.0 * max_thrust));
+        d.gnd_hclip = (float)(0.25 * pr * sqrt((15.0 * max_rpm * max_rpm * kf * gnd) / max_thrust));
+    }
+    d.seed_lo = (uint32_t)seed; d.seed_hi = (uint32_t)(seed >> 32);
+    d.gid_base = gid_base;
+    return CF_OK;
+}
+
+void begin_timing(cf_env* e, cudaStream_t st, EventPair** out) {
+    *out = nullptr;
+    if (!e->timing) return;
+    if (e->ev_used == e->ev_pool.size()) {
+        if (e->ev_pool.size() >= 8192) return;
+        EventPair p;
+        if (cudaEventCreate(&p.a) != cudaSuccess || cudaEventCreate(&p.b) != cudaSuccess) return;
+        e->ev_pool.push_back(p);
+    }
+    *out = &e->ev_pool[e->ev_used++];
+    cudaEventRecord((*out)->a, st);
+}
+void end_timing(EventPair* p, cudaStream_t st) {
+    if (p) cudaEventRecord(p->b, st);
+}
+void drain_timing(cf_env* e) {
+    for (size_t i = 0; i < e->ev_used; ++i) {
+        float ms = 0.f;
+        cudaEventSynchronize(e->ev_pool[i].b);
+        if (cudaEventElapsedTime(&ms, e->ev_pool[i].a, e->ev_pool[i].b) == cudaSuccess) { e->ev_ms += ms; e->ev_count += 1; }
+    }
+    e->ev_used = 0;
+}
+
+int check_tables(cf_env* e) {
+    const cf_config& c = e->cfg;
+    auto have = [&](int li) { return c.hj_mode == CF_HJ_SIGN_TABLE ? e->signs_dev[li] != nullptr : e->value_dev[li] != nullptr; };
+    if (c.disturbance_kind == CF_DSTB_HJ_FIXED) {
+        int li = e->dev.fixed_level_idx;
+        if (li > 0 && !have(li)) return fail(CF_ERR_NO_TABLE, "no HJ value table loaded for level index %s%lld", "", li);
+    } else if (c.disturbance_kind == CF_DSTB_HJ_BOLTZMANN) {
+        for (int li = 1; li <= 20; ++li)
+            if (!have(li)) return fail(CF_ERR_NO_TABLE, "no HJ value table loaded for level index %s%lld", "", li);
+    }
+    return CF_OK;
+}
+
+int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint8_t* done, float* cost,
+                float* term_obs, uint8_t* truncated, cudaStream_t st) {
+    if (!e || !act || !obs || !rew || !done || k < 1) return fail(CF_ERR_INVALID, "cf_step: null argument%s", "");
+    int rc = check_tables(e);
+    if (rc != CF_OK) return rc;
+    if (e->dev.injected && (!e->inj[0] || !e->inj[1] || (e->dev.auto_reset && (!e->inj[2] || !e->inj[3]))))
+        return fail(CF_ERR_INVALID, "rng_mode INJECTED: call cf_set_noise_override first%s", "");
+    CU(cudaSetDevice(e->device));
+    StepIO io;
+    io.act = act; io.obs = obs; io.rew = rew; io.done = done; io.cost = cost;
+    io.term_obs = term_obs; io.truncated = truncated;
+    io.inj_step_z = e->inj[0]; io.inj_step_u = e->inj[1]; io.inj_reset_z = e->inj[2]; io.inj_reset_u = e->inj[3];
+    io.fin_ret = e->fin_ret; io.fin_len = e->fin_len; io.agg = e->agg;
+    EventPair* ep;
+    begin_timing(e, st, &ep);
+    launch_step(e->S, e->n, k, e->dev, e->tab, io, st);
+    end_timing(ep, st);
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
+template <typename T>
+int ensure(T** p, size_t count) {
+    if (*p) return CF_OK;
+    cudaError_t err = cudaMalloc((void**)p, count * sizeof(T));
+    if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc"); return CF_ERR_ALLOC; }
+    return CF_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* cf_last_error(void) { return g_err; }
+int cf_abi_version(void) { return CF_ABI_VERSION; }
+
+int cf_config_default(const char* env_id, cf_config* c) {
+    if (!env_id || !c) return fail(CF_ERR_INVALID, "cf_config_default: null argument%s", "");
+    const IdDefaults* d = nullptr;
+    for (const IdDefaults& k : kIds)
+        if (strcmp(k.id, env_id) == 0) d = &k;
+    if (!d) return fail(CF_ERR_INVALID, "unknown env id '%s'", env_id);
+    memset(c, 0, sizeof(*c));
+    c->abi_version = CF_ABI_VERSION;
+    c->reward_kind = d->reward; c->disturbance_kind = d->dstb;
+    c->observation_noise = 1; c->enable_reset_distribution = 1;          // base.py:26-47
+    c->aggregate_phy_steps = 2; c->max_episode_steps = 500;              // __init__.py max_episode_steps
+    c->gyroscopic = 1; c->use_ground_effect = 0;                         // physics.py:18,25
+    c->hj_mode = CF_HJ_SIGN_TABLE; c->rng_mode = CF_RNG_PHILOX; c->auto_reset = 1;
+    c->domain_randomization = 0.10; c->disturbance_level = d->level;
+    if (d->reward == CF_REWARD_FREE) {                                   // hover_free.py:29-34
+        c->penalty_action = 0.0; c->penalty_angle = 1.0; c->penalty_spin = 1.0;
+        c->penalty_terminal = 1000.0; c->penalty_velocity = 1.0; c->penalty_z = 0.0;
+    } else {                                                             // hover.py:28-32
+        c->penalty_action = 1e-4; c->penalty_angle = 0.0; c->penalty_spin = 1e-4;
+        c->penalty_terminal = 1000.0; c->penalty_velocity = 0.0; c->penalty_z = 0.0;
+    }
+    c->done_roll_pitch_rad = deg2rad(d->rp_deg); c->done_rate_deg = d->rate_deg;
+    c->init_pos_lim = 0.25; c->init_angle = d->init_angle; c->init_yaw = 2.0 * kPiD;   // hover_free.py:249-274
+    c->init_vel_lim = 0.1; c->init_rate_lim = deg2rad(d->cost_rate_deg); c->init_yaw_rate_lim = deg2rad(20.0);
+    c->cost_rate_limit = deg2rad(d->cost_rate_deg);                      // rpy_dot_limit, hover_free.py:75 / hover.py:1317
+    c->sim_time_step = 1.0 / 200.0; c->motor_time_constant = 0.080;
+    c->motor_thrust_noise = 0.05; c->latency = 0.015;
+    c->linear_damping = 0.04; c->angular_damping = 0.04;
+    return CF_OK;
+}
+
+int cf_create(const cf_config* cfg, int32_t n_envs, int32_t device, uint64_t seed, int64_t env_id_base, cf_env** out) {
+    if (!cfg || !out || n_envs < 1) return fail(CF_ERR_INVALID, "cf_create: bad argument%s", "");
+    *out = nullptr;
+    DevCfg dev;
+    int rc = derive(*cfg, seed, env_id_base, dev);
+    if (rc != CF_OK) return rc;
+    int count = 0;
+    CU(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) return fail(CF_ERR_INVALID, "no CUDA device %s%lld", "", device);
+    CU(cudaSetDevice(device));
+    cf_env* e = new (std::nothrow) cf_env();
+    if (!e) return fail(CF_ERR_ALLOC, "out of host memory%s", "");
+    e->cfg = *cfg; e->dev = dev; e->n = n_envs; e->device = device; e->obs_dim = dev.obs_dim;
+    memset(&e->tab, 0, sizeof(e->tab));
+    double grid[6][CF_HJ_PTS], dx[6], cdf[21];
+    grid_tables(grid, dx, cdf);
+    cudaError_t err = upload_constants(grid, dx, cdf);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->S, sizeof(float4) * kGroups * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_ret, sizeof(float) * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_len, sizeof(int) * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->agg, sizeof(double) * 4);
+    if (err == cudaSuccess) err = cudaMemset(e->fin_ret, 0, sizeof(float) * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMemset(e->fin_len, 0, sizeof(int) * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMemset(e->agg, 0, sizeof(double) * 4);
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) { launch_init(e->S, n_envs, e->dev, 0); e->launches += 1; err = cudaDeviceSynchronize(); }
+    if (err != cudaSuccess) { cuda_fail(err, "cf_create"); cf_destroy(e); return err == cudaErrorMemoryAllocation ? CF_ERR_ALLOC : CF_ERR_CUDA; }
+    *out = e;
+    return CF_OK;
+}
+
+int cf_destroy(cf_env* e) {
+    if (!e) return CF_OK;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
+    for (int i = 0; i < 4; ++i) cudaFree(e->inj[i]);
+    cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
+    cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
+    cudaFree(e->d_done); cudaFree(e->d_trunc); cudaFree(e->d_mask);
+    for (EventPair& p : e->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    if (e->hstream) cudaStreamDestroy(e->hstream);
+    delete e;
+    return CF_OK;
+}
+
+int cf_obs_dim(const cf_env* e) { return e ? e->obs_dim : CF_ERR_INVALID; }
+int cf_num_envs(const cf_env* e) { return e ? e->n : CF_ERR_INVALID; }
+int64_t cf_launch_count(const cf_env* e) { return e ? e->launches : 0; }
+
+int cf_load_hj_table(cf_env* e, int32_t li, const float* V_host) {
+    if (!e || !V_host || li < 0 || li >= CF_MAX_LEVELS) return fail(CF_ERR_INVALID, "cf_load_hj_table: bad argument%s", "");
+    CU(cudaSetDevice(e->device));
+    const size_t vbytes = sizeof(float) * (size_t)CF_HJ_CELLS, pbytes = (CF_HJ_CELLS + 3) / 4;
+    float* V = e->value_dev[li];
+    if (!V) { cudaError_t err = cudaMalloc((void**)&V, vbytes); if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc(value table)"); return CF_ERR_ALLOC; } }
+    CU(cudaMemcpy(V, V_host, vbytes, cudaMemcpyHostToDevice));
+    int rc = ensure(&e->signs_dev[li], pbytes);
+    if (rc != CF_OK) { if (!e->value_dev[li]) cudaFree(V); return rc; }
+    launch_hj_signs(V, e->signs_dev[li], 0);
+    e->launches += 1;
+    CU(cudaDeviceSynchronize());
+    if (e->cfg.hj_mode == CF_HJ_SIGN_TABLE) { cudaFree(V); V = nullptr; }   // 2.85 MB/level stays, 45.6 MB/level goes
+    e->value_dev[li] = V;
+    e->tab.value[li] = V; e->tab.signs[li] = e->signs_dev[li];
+    return CF_OK;
+}
+
+int cf_get_hj_signs(cf_env* e, int32_t li, uint8_t* out_host) {
+    if (!e || !out_host || li < 0 || li >= CF_MAX_LEVELS) return fail(CF_ERR_INVALID, "cf_get_hj_signs: bad argument%s", "");
+    if (!e->signs_dev[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
+    CU(cudaSetDevice(e->device));
+    CU(cudaMemcpy(out_host, e->signs_dev[li], (CF_HJ_CELLS + 3) / 4, cudaMemcpyDeviceToHost));
+    return CF_OK;
+}
+
+int cf_reset_dev(cf_env* e, const uint8_t* mask, float* obs, void* stream) {
+    if (!e || !obs) return fail(CF_ERR_INVALID, "cf_reset: null argument%s", "");
+    if (e->dev.injected && (!e->inj[2] || !e->inj[3])) return fail(CF_ERR_INVALID, "rng_mode INJECTED: call cf_set_noise_override first%s", "");
+    CU(cudaSetDevice(e->device));
+    launch_reset(e->S, e->n, e->dev, mask, obs, e->inj[2], e->inj[3], (cudaStream_t)stream);
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
+int cf_step_dev(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
+                uint8_t* truncated, void* stream) {
+    return step_common(e, 1, act, obs, rew, done, cost, term_obs, truncated, (cudaStream_t)stream);
+}
+
+int cf_step_k_dev(cf_env* e, int32_t k, const float* act, float* obs, float* rew, uint8_t* done, float* cost, void* stream) {
+    if (e && e->dev.injected && k != 1) return fail(CF_ERR_INVALID, "cf_step_k: injected noise supports k = 1 only%s", "");
+    return step_common(e, k, act, obs, rew, done, cost, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+int cf_reset_host(cf_env* e, const uint8_t* mask, float* obs) {
+    if (!e || !obs) return fail(CF_ERR_INVALID, "cf_reset: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    const size_t n = e->n, od = e->obs_dim;
+    int rc = ensure(&e->d_obs, n * od);
+    if (rc == CF_OK && mask) rc = ensure(&e->d_mask, n);
+    if (rc != CF_OK) return rc;
+    cudaStream_t st = e->hstream;
+    if (mask) {
+        CU(cudaMemcpyAsync(e->d_mask, mask, n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(e->d_obs, obs, n * od * sizeof(float), cudaMemcpyHostToDevice, st));   // keep unmasked rows
+    }
+    rc = cf_reset_dev(e, mask ? e->d_mask : nullptr, e->d_obs, st);
+    if (rc != CF_OK) return rc;
+    CU(cudaMemcpyAsync(obs, e->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return CF_OK;
+}
+
+int cf_step_host(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
+                 uint8_t* truncated) {
+    if (!e || !act || !obs || !rew || !done) return fail(CF_ERR_INVALID, "cf_step: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    const size_t n = e->n, od = e->obs_dim;
+    int rc = ensure(&e->d_act, n * 4);
+    if (rc == CF_OK) rc = ensure(&e->d_obs, n * od);
+    if (rc == CF_OK) rc = ensure(&e->d_rew, n);
+    if (rc == CF_OK) rc = ensure(&e->d_done, n);
+    if (rc == CF_OK && cost) rc = ensure(&e->d_cost, n);
+    if (rc == CF_OK && term_obs) rc = ensure(&e->d_term, n * od);
+    if (rc == CF_OK && truncated) rc = ensure(&e->d_trunc, n);
+    if (rc != CF_OK) return rc;
+    cudaStream_t st = e->hstream;
+    // pinned caller buffers make these true async DMA transfers; pageable ones are staged by the driver
+    CU(cudaMemcpyAsync(e->d_act, act, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (term_obs) CU(cudaMemcpyAsync(e->d_term, term_obs, n * od * sizeof(float), cudaMemcpyHostToDevice, st));
+    rc = step_common(e, 1, e->d_act, e->d_obs, e->d_rew, e->d_done, cost ? e->d_cost : nullptr,
+                     term_obs ? e->d_term : nullptr, truncated ? e->d_trunc : nullptr, st);
+    if (rc != CF_OK) return rc;
+    CU(cudaMemcpyAsync(obs, e->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(rew, e->d_rew, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(done, e->d_done, n, cudaMemcpyDeviceToHost, st));
+    if (cost) CU(cudaMemcpyAsync(cost, e->d_cost, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (term_obs) CU(cudaMemcpyAsync(term_obs, e->d_term, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (truncated) CU(cudaMemcpyAsync(truncated, e->d_trunc, n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return CF_OK;
+}
+
+int cf_get_state(cf_env* e, float* state_host) {
+    if (!e || !state_host) return fail(CF_ERR_INVALID, "cf_get_state: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure(&e->rec_dev, (size_t)kGroups * e->n);
+    if (rc != CF_OK) return rc;
+    CU(cudaDeviceSynchronize());
+    launch_unpack_state(e->S, e->n, e->rec_dev, 0);
+    e->launches += 1;
+    CU(cudaMemcpy(state_host, e->rec_dev, sizeof(float4) * kGroups * (size_t)e->n, cudaMemcpyDeviceToHost));
+    return CF_OK;
+}
+
+int cf_set_state(cf_env* e, const float* state_host) {
+    if (!e || !state_host) return fail(CF_ERR_INVALID, "cf_set_state: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure(&e->rec_dev, (size_t)kGroups * e->n);
+    if (rc != CF_OK) return rc;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(e->rec_dev, state_host, sizeof(float4) * kGroups * (size_t)e->n, cudaMemcpyHostToDevice));
+    launch_pack_state(e->S, e->n, e->rec_dev, 0);
+    e->launches += 1;
+    CU(cudaDeviceSynchronize());
+    return CF_OK;
+}
+
+int cf_get_levels(cf_env* e, float* levels_host) {
+    if (!e || !levels_host) return fail(CF_ERR_INVALID, "cf_get_levels: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure(&e->d_rew, (size_t)e->n);
+    if (rc != CF_OK) return rc;
+    CU(cudaDeviceSynchronize());
+    launch_levels(e->S, e->n, e->d_rew, 0);
+    e->launches += 1;
+    CU(cudaMemcpy(levels_host, e->d_rew, sizeof(float) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    return CF_OK;
+}
+
+int cf_set_noise_override(cf_env* e, const float* sz, const float* su, const float* rz, const float* ru) {
+    if (!e) return fail(CF_ERR_INVALID, "cf_set_noise_override: null handle%s", "");
+    CU(cudaSetDevice(e->device));
+    const float* src[4] = {sz, su, rz, ru};
+    const size_t slots[4] = {CF_STEP_NORMALS, CF_STEP_UNIFORMS, CF_RESET_NORMALS, CF_RESET_UNIFORMS};
+    CU(cudaDeviceSynchronize());
+    for (int i = 0; i < 4; ++i) {
+        if (!src[i]) continue;
+        int rc = ensure(&e->inj[i], slots[i] * (size_t)e->n);
+        if (rc != CF_OK) return rc;
+        CU(cudaMemcpy(e->inj[i], src[i], sizeof(float) * slots[i] * (size_t)e->n, cudaMemcpyHostToDevice));
+    }
+    return CF_OK;
+}
+
+int cf_hj_lookup_host(cf_env* e, int32_t li, const double* states, int32_t n, int32_t* idx, float* dstb_sign) {
+    if (!e || !states || !idx || !dstb_sign || n < 1 || li < 0 || li >= CF_MAX_LEVELS)
+        return fail(CF_ERR_INVALID, "cf_hj_lookup_host: bad argument%s", "");
+    const bool use_value = e->cfg.hj_mode == CF_HJ_VALUE_TABLE;
+    if (use_value ? !e->value_dev[li] : !e->signs_dev[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
+    CU(cudaSetDevice(e->device));
+    double* ds = nullptr; int* di = nullptr; float* dd = nullptr;
+    cudaError_t err = cudaMalloc((void**)&ds, sizeof(double) * 6 * (size_t)n);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&di, sizeof(int) * 6 * (size_t)n);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&dd, sizeof(float) * 2 * (size_t)n);
+    if (err == cudaSuccess) err = cudaMemcpy(ds, states, sizeof(double) * 6 * (size_t)n, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) {
+        launch_hj_lookup(ds, n, use_value ? e->value_dev[li] : nullptr, use_value ? nullptr : e->signs_dev[li], di, dd, 0);
+        e->launches += 1;
+        err = cudaMemcpy(idx, di, sizeof(int) * 6 * (size_t)n, cudaMemcpyDeviceToHost);
+    }
+    if (err == cudaSuccess) err = cudaMemcpy(dstb_sign, dd, sizeof(float) * 2 * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaFree(ds); cudaFree(di); cudaFree(dd);
+    if (err != cudaSuccess) return cuda_fail(err, "cf_hj_lookup_host");
+    return CF_OK;
+}
+
+int cf_episode_stats(cf_env* e, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host) {
+    if (!e || !out) return fail(CF_ERR_INVALID, "cf_episode_stats: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(out, e->agg, sizeof(double) * 4, cudaMemcpyDeviceToHost));
+    if (fin_ret_host) CU(cudaMemcpy(fin_ret_host, e->fin_ret, sizeof(float) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    if (fin_len_host) CU(cudaMemcpy(fin_len_host, e->fin_len, sizeof(int) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    if (reset) CU(cudaMemset(e->agg, 0, sizeof(double) * 4));
+    return CF_OK;
+}
+
+int cf_gae_dev(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
+               float gamma, float lam, float rew_scale, int32_t T, int32_t N, float* adv, float* target_v,
+               float* disc_ret, void* stream) {
+    if (!rew || !val || !done || !last_val || !adv || !target_v || !disc_ret || T < 1 || N < 1)
+        return fail(CF_ERR_INVALID, "cf_gae: bad argument%s", "");
+    launch_gae(rew, val, done, end_val, last_val, gamma, lam, rew_scale, T, N, adv, target_v, disc_ret, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
+int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
+                float gamma, float lam, float rew_scale, int32_t T, int32_t N, float* adv, float* target_v,
+                float* disc_ret) {
+    if (!rew || !val || !done || !last_val || !adv || !target_v || !disc_ret || T < 1 || N < 1)
+        return fail(CF_ERR_INVALID, "cf_gae: bad argument%s", "");
+    const size_t tn = (size_t)T * N;
+    float *d_f = nullptr; uint8_t* d_d = nullptr;
+    // one slab: rew, val, end_val, adv, tgt, ret [T*N each] + last_val [N]
+    cudaError_t err = cudaMalloc((void**)&d_f, sizeof(float) * (6 * tn + N));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&d_d, tn);
+    float *d_rew = d_f, *d_val = d_f + tn, *d_end = d_f + 2 * tn, *d_adv = d_f + 3 * tn, *d_tgt = d_f + 4 * tn,
+          *d_ret = d_f + 5 * tn, *d_last = d_f + 6 * tn;
+    if (err == cudaSuccess) err = cudaMemcpy(d_rew, rew, sizeof(float) * tn, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMemcpy(d_val, val, sizeof(float) * tn, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess && end_val) err = cudaMemcpy(d_end, end_val, sizeof(float) * tn, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMemcpy(d_last, last_val, sizeof(float) * N, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMemcpy(d_d, done, tn, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) {
+        launch_gae(d_rew, d_val, d_d, end_val ? d_end : nullptr, d_last, gamma, lam, rew_scale, T, N, d_adv, d_tgt, d_ret, 0);
+        err = cudaMemcpy(adv, d_adv, sizeof(float) * tn, cudaMemcpyDeviceToHost);
+    }
+    if (err == cudaSuccess) err = cudaMemcpy(target_v, d_tgt, sizeof(float) * tn, cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess) err = cudaMemcpy(disc_ret, d_ret, sizeof(float) * tn, cudaMemcpyDeviceToHost);
+    cudaFree(d_f); cudaFree(d_d);
+    if (err != cudaSuccess) return cuda_fail(err, "cf_gae_host");
+    return CF_OK;
+}
+
+int cf_kernel_timing(cf_env* e, int32_t enable, int32_t reset, double* avg_ms, int64_t* launches) {
+    if (!e) return fail(CF_ERR_INVALID, "cf_kernel_timing: null handle%s", "");
+    CU(cudaSetDevice(e->device));
+    drain_timing(e);
+    if (avg_ms) *avg_ms = e->ev_count ? e->ev_ms / (double)e->ev_count : 0.0;
+    if (launches) *launches = e->ev_count;
+    if (reset) { e->ev_ms = 0.0; e->ev_count = 0; }
+    e->timing = enable != 0;
+    return CF_OK;
+}
+
+void* cf_host_alloc(uint64_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cuda_fail(cudaGetLastError(), "cudaHostAlloc"); return nullptr; }
+    return p;
+}
+void cf_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+}  // extern "C"

@@ -1,0 +1,332 @@
+"""Batched CrazyFlie hover environment: the Python host side above the C ABI.
+
+Mirrors the gym interface of the reference envs (``reset`` / ``step`` / ``observation_space``
+/ ``action_space`` / ``disturbance_level`` / ``_max_episode_steps`` / ``seed`` / ``close``;
+envs/base.py:139-148, 420-507 and the step overrides of envs/hover_free.py, envs/hover.py)
+for ``num_envs`` independent envs whose state lives in HBM.  PyTorch is used for device
+memory and streams only; all arithmetic is in ``csrc/`` (hand-written sm_100a CUDA).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import abi
+from .hj_tables import LEVELS, level_index, load_table
+
+#: ids registered by phoenix_drone_simulation/__init__.py that this package implements
+ENV_IDS = (
+    'DroneHoverBulletFreeEnvWithoutAdversary-v0',
+    'DroneHoverBulletFreeEnvWithAdversary-v0',
+    'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0',
+    'DroneHoverBulletEnv-v0',
+    'DroneHoverBulletEnvWithoutAdversary-v0',
+    'DroneHoverBulletEnvWithAdversary-v0',
+    'DroneHoverBulletEnvWithRandomHJAdversary-v0',
+    'DroneHoverBulletEnvWithCurriculumHJAdversary-v0',
+    'DroneHoverBulletEnvWithRandomAdversary-v0',
+    'DroneHoverBulletEnvWithAdversaryInitial-v0',
+)
+
+# constructor kwargs of the reference env classes accepted by make() (base.py:26-47,
+# hover_free.py:18-39) -> cf_config field
+_KWARGS = {
+    'observation_noise': 'observation_noise', 'domain_randomization': 'domain_randomization',
+    'enable_reset_distribution': 'enable_reset_distribution', 'aggregate_phy_steps': 'aggregate_phy_steps',
+    'latency': 'latency', 'motor_time_constant': 'motor_time_constant', 'motor_thrust_noise': 'motor_thrust_noise',
+    'penalty_action': 'penalty_action', 'penalty_angle': 'penalty_angle', 'penalty_spin': 'penalty_spin',
+    'penalty_terminal': 'penalty_terminal', 'penalty_velocity': 'penalty_velocity', 'penalty_z': 'penalty_z',
+    'disturbance_level': 'disturbance_level', 'max_episode_steps': 'max_episode_steps',
+    # switches of this implementation
+    'use_ground_effect': 'use_ground_effect', 'gyroscopic': 'gyroscopic', 'hj_mode': 'hj_mode',
+    'rng_mode': 'rng_mode', 'auto_reset': 'auto_reset', 'linear_damping': 'linear_damping',
+    'angular_damping': 'angular_damping',
+}
+
+
+@dataclass
+class Box:
+    """Minimal stand-in for gym.spaces.Box (gym is not a dependency)."""
+    low: np.ndarray
+    high: np.ndarray
+    shape: tuple
+    dtype: type = np.float32
+
+    def sample(self) -> np.ndarray:
+        return np.random.uniform(self.low, self.high).astype(self.dtype)
+
+    def contains(self, x) -> bool:
+        x = np.asarray(x)
+        return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class CrazyFlieVecEnv:
+    """``num_envs`` reference hover envs stepped by one CUDA kernel launch.
+
+    ``reset() -> obs[N, obs_dim]``; ``step(act[N,4]) -> (obs, rew[N], done[N] bool, info)`` with
+    device tensors.  Done envs are reset inside the step (``auto_reset``); ``info`` carries
+    ``cost``, ``disturbance_level`` (lazy), ``truncated`` (``TimeLimit.truncated``) and
+    ``terminal_observation`` for the envs that finished.
+    """
+
+    def __init__(self, env_id: str, num_envs: int = 1, device: Optional[int] = None, seed: int = 0,
+                 env_id_base: int = 0, hj_table_dir: Optional[str] = None, hj_table_seed: int = 15,
+                 return_terminal_obs: bool = False, **kwargs):
+        L = abi.lib()
+        if not torch.cuda.is_available():
+            raise RuntimeError('CrazyFlieVecEnv needs a CUDA device (no CPU fallback)')
+        self.id = env_id
+        self.num_envs = int(num_envs)
+        self.device_index = torch.cuda.current_device() if device is None else int(device)
+        self.device = torch.device('cuda', self.device_index)
+        cfg = abi.config_default(env_id)
+        for k, v in kwargs.items():
+            if k not in _KWARGS:
+                raise TypeError(f'unsupported env kwarg {k!r}')
+            field = _KWARGS[k]
+            ftype = dict(abi.CfConfig._fields_)[field]
+            setattr(cfg, field, int(v) if ftype is C.c_int32 else float(v))
+        self.cfg = cfg
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            abi.check(L.cf_create(C.byref(cfg), self.num_envs, self.device_index, int(seed) & (2 ** 64 - 1),
+                                  int(env_id_base), C.byref(self._h)))
+        self._L = L
+        self.obs_dim = L.cf_obs_dim(self._h)
+        # spaces as in envs/base.py:139-148
+        self.observation_space = Box(-1000.0 * np.ones(self.obs_dim, np.float32), 1000.0 * np.ones(self.obs_dim, np.float32),
+                                     (self.obs_dim,))
+        self.action_space = Box(-np.ones(4, np.float32), np.ones(4, np.float32), (4,))
+        self._max_episode_steps = cfg.max_episode_steps
+        n, od = self.num_envs, self.obs_dim
+        self._obs = torch.empty((n, od), dtype=torch.float32, device=self.device)
+        self._rew = torch.empty((n,), dtype=torch.float32, device=self.device)
+        self._done = torch.empty((n,), dtype=torch.uint8, device=self.device)
+        self._cost = torch.empty((n,), dtype=torch.float32, device=self.device)
+        self._trunc = torch.empty((n,), dtype=torch.uint8, device=self.device)
+        self._term = torch.zeros((n, od), dtype=torch.float32, device=self.device) if return_terminal_obs else None
+        self._load_tables(hj_table_dir, hj_table_seed)
+
+    # ------------------------------------------------------------------ tables
+    def _needed_levels(self):
+        kind = self.cfg.disturbance_kind
+        if kind == abi.CF_DSTB_HJ_FIXED:
+            li = level_index(self.cfg.disturbance_level)
+            return [li] if li > 0 else []
+        if kind == abi.CF_DSTB_HJ_BOLTZMANN:
+            return [level_index(l) for l in LEVELS if l > 0]
+        return []
+
+    def _load_tables(self, table_dir, seed):
+        for li in self._needed_levels():
+            self.load_hj_table(li / 10.0, load_table(li / 10.0, table_dir, seed))
+
+    def load_hj_table(self, level: float, V: np.ndarray) -> None:
+        """np.load(fastrack_{level}_15x15.npy) of distur_gener.py:155, hoisted out of the step."""
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        if V.shape != (15,) * 6:
+            raise ValueError(f'value table must have shape (15,)*6, got {V.shape}')
+        abi.check(self._L.cf_load_hj_table(self._h, level_index(level), V.ctypes.data_as(C.c_void_p)))
+
+    # ------------------------------------------------------------------ gym surface
+    def seed(self, seed=None):
+        """gym 0.19 Env.seed is a no-op in the reference (iwpg.py:138); the RNG key is fixed at make()."""
+        return
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def reset(self, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        m = None
+        if mask is not None:
+            m = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        abi.check(self._L.cf_reset_dev(self._h, _ptr(m), _ptr(self._obs), self._stream()))
+        return self._obs
+
+    def step(self, action: torch.Tensor):
+        act = action.to(device=self.device, dtype=torch.float32).contiguous()
+        if act.shape != (self.num_envs, 4):
+            raise ValueError(f'action must have shape ({self.num_envs}, 4), got {tuple(act.shape)}')
+        abi.check(self._L.cf_step_dev(self._h, _ptr(act), _ptr(self._obs), _ptr(self._rew), _ptr(self._done),
+                                      _ptr(self._cost), _ptr(self._term), _ptr(self._trunc), self._stream()))
+        info = {'cost': self._cost, 'truncated': self._trunc.bool()}
+        if self._term is not None:
+            info['terminal_observation'] = self._term
+        return self._obs, self._rew, self._done.bool(), info
+
+    def step_k(self, actions: torch.Tensor, obs: Optional[torch.Tensor] = None, rew: Optional[torch.Tensor] = None,
+               done: Optional[torch.Tensor] = None, cost: Optional[torch.Tensor] = None):
+        """K control steps in one launch (state stays in registers): actions [K, N, 4] ->
+        obs [K, N, obs_dim], rew / done(uint8) / cost [K, N]."""
+        act = actions.to(device=self.device, dtype=torch.float32).contiguous()
+        k = act.shape[0]
+        if act.shape != (k, self.num_envs, 4):
+            raise ValueError('actions must have shape (K, num_envs, 4)')
+        n, od = self.num_envs, self.obs_dim
+        obs = torch.empty((k, n, od), dtype=torch.float32, device=self.device) if obs is None else obs
+        rew = torch.empty((k, n), dtype=torch.float32, device=self.device) if rew is None else rew
+        done = torch.empty((k, n), dtype=torch.uint8, device=self.device) if done is None else done
+        cost = torch.empty((k, n), dtype=torch.float32, device=self.device) if cost is None else cost
+        abi.check(self._L.cf_step_k_dev(self._h, k, _ptr(act), _ptr(obs), _ptr(rew), _ptr(done), _ptr(cost), self._stream()))
+        return obs, rew, done, cost
+
+    @property
+    def disturbance_level(self) -> np.ndarray:
+        out = np.empty(self.num_envs, np.float32)
+        abi.check(self._L.cf_get_levels(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def render(self, mode='human'):
+        raise NotImplementedError('graphics (PyBullet GUI / OpenGL camera, envs/base.py:343-418) is unavailable on this box')
+
+    capture_image = render
+
+    # ------------------------------------------------------------------ state / parity hooks
+    def get_state(self) -> np.ndarray:
+        out = np.empty((self.num_envs, abi.CF_STATE_WORDS), np.float32)
+        abi.check(self._L.cf_get_state(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def set_state(self, rec: np.ndarray) -> None:
+        rec = np.ascontiguousarray(rec, dtype=np.float32)
+        assert rec.shape == (self.num_envs, abi.CF_STATE_WORDS)
+        abi.check(self._L.cf_set_state(self._h, rec.ctypes.data_as(C.c_void_p)))
+
+    def set_noise_override(self, step_z=None, step_u=None, reset_z=None, reset_u=None) -> None:
+        arrs = []
+        for a, slots in ((step_z, abi.CF_STEP_NORMALS), (step_u, abi.CF_STEP_UNIFORMS),
+                         (reset_z, abi.CF_RESET_NORMALS), (reset_u, abi.CF_RESET_UNIFORMS)):
+            if a is None:
+                arrs.append(None)
+                continue
+            a = np.ascontiguousarray(a, dtype=np.float32)
+            assert a.shape == (slots, self.num_envs), (a.shape, slots)
+            arrs.append(a)
+        abi.check(self._L.cf_set_noise_override(
+            self._h, *[None if a is None else a.ctypes.data_as(C.c_void_p) for a in arrs]))
+
+    def hj_lookup(self, level: float, states: np.ndarray):
+        """Grid indices and (+1/-1) signs of the optimal roll/pitch disturbance for float64 states [n, 6]."""
+        s = np.ascontiguousarray(states, dtype=np.float64)
+        n = s.shape[0]
+        idx = np.empty((n, 6), np.int32)
+        sign = np.empty((n, 2), np.float32)
+        abi.check(self._L.cf_hj_lookup_host(self._h, level_index(level), s.ctypes.data_as(C.c_void_p), n,
+                                            idx.ctypes.data_as(C.c_void_p), sign.ctypes.data_as(C.c_void_p)))
+        return idx, sign
+
+    def episode_stats(self, reset: bool = False) -> dict:
+        out = (C.c_double * 4)()
+        abi.check(self._L.cf_episode_stats(self._h, int(reset), out, None, None))
+        n = out[0]
+        return {'episodes': int(n), 'return_sum': out[1], 'length_sum': out[2],
+                'mean_return': out[1] / n if n else float('nan'), 'mean_length': out[2] / n if n else float('nan')}
+
+    def kernel_timing(self, enable: bool, reset: bool = False):
+        ms, cnt = C.c_double(), C.c_int64()
+        abi.check(self._L.cf_kernel_timing(self._h, int(enable), int(reset), C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.cf_launch_count(self._h))
+
+    # host-pointer API (NumPy in / NumPy out), what a gym-style caller uses
+    def reset_host(self, obs: np.ndarray, mask: Optional[np.ndarray] = None) -> np.ndarray:
+        abi.check(self._L.cf_reset_host(self._h, None if mask is None else mask.ctypes.data_as(C.c_void_p),
+                                        obs.ctypes.data_as(C.c_void_p)))
+        return obs
+
+    def step_host(self, act, obs, rew, done, cost=None, term_obs=None, truncated=None):
+        p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        abi.check(self._L.cf_step_host(self._h, p(act), p(obs), p(rew), p(done), p(cost), p(term_obs), p(truncated)))
+
+    def close(self):
+        if getattr(self, '_h', None) is not None and self._h.value:
+            self._L.cf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class GymAdapter:
+    """Single-env adapter with the reference's gym signature (NumPy in/out), so that the rollout
+    loop of algs/iwpg/iwpg.py:372-410 runs unmodified: ``reset() -> ndarray[obs_dim]``,
+    ``step(a) -> (obs, float, bool, dict)``; like gym's TimeLimit it does not auto-reset."""
+
+    def __init__(self, env_id: str, **kwargs):
+        kwargs = dict(kwargs)
+        kwargs['auto_reset'] = 0
+        self.vec = CrazyFlieVecEnv(env_id, num_envs=1, **kwargs)
+        self.id = env_id
+        self.observation_space, self.action_space = self.vec.observation_space, self.vec.action_space
+        self._max_episode_steps = self.vec._max_episode_steps
+        od = self.vec.obs_dim
+        self._obs, self._act = np.zeros((1, od), np.float32), np.zeros((1, 4), np.float32)
+        self._rew, self._done = np.zeros(1, np.float32), np.zeros(1, np.uint8)
+        self._cost, self._trunc = np.zeros(1, np.float32), np.zeros(1, np.uint8)
+
+    @property
+    def unwrapped(self):
+        return self
+
+    @property
+    def disturbance_level(self) -> float:
+        return float(self.vec.disturbance_level[0])
+
+    def seed(self, seed=None):
+        return
+
+    def reset(self) -> np.ndarray:
+        self.vec.reset_host(self._obs)
+        return self._obs[0].astype(np.float64)
+
+    def step(self, action):
+        self._act[0] = np.asarray(action, dtype=np.float32)
+        self.vec.step_host(self._act, self._obs, self._rew, self._done, self._cost, None, self._trunc)
+        info = {'cost': float(self._cost[0]), 'disturbance_level': self.disturbance_level}
+        if self._trunc[0]:
+            info['TimeLimit.truncated'] = True
+        return self._obs[0].astype(np.float64), float(self._rew[0]), bool(self._done[0]), info
+
+    def render(self, mode='human'):
+        return self.vec.render(mode)
+
+    def close(self):
+        self.vec.close()
+
+
+def make(env_id: str, num_envs: Optional[int] = None, **kwargs):
+    """``gym.make(id, **kwargs)`` of the reference (iwpg.py:76-77).  With ``num_envs`` it returns
+    the batched :class:`CrazyFlieVecEnv`; without, the single-env :class:`GymAdapter`."""
+    if env_id not in ENV_IDS:
+        raise KeyError(f'unknown env id {env_id!r}; implemented: {ENV_IDS}')
+    if num_envs is None:
+        return GymAdapter(env_id, **kwargs)
+    return CrazyFlieVecEnv(env_id, num_envs=num_envs, **kwargs)
+
+
+def register_with_gym() -> int:
+    """Register the ids with gym / gymnasium when one is importable (neither is a dependency)."""
+    count = 0
+    for modname in ('gym', 'gymnasium'):
+        try:
+            mod = __import__(modname)
+            for env_id in ENV_IDS:
+                mod.register(id=env_id, entry_point=lambda _id=env_id, **kw: GymAdapter(_id, **kw), max_episode_steps=500)
+                count += 1
+        except Exception:
+            continue
+    return count

@@ -197,6 +197,16 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
                 const float* last_val, float gamma, float lam, float rew_scale,
                 int32_t T, int32_t N, float* adv, float* target_v, float* disc_ret);
 
+/* ---- episode statistics (what the reference logs per finished episode, loggers.py:612-633) -- */
+/* out[0..3] = episodes finished, sum of their returns, sum of their lengths, spare - accumulated
+ * on the device since creation or the last call with reset != 0.  fin_ret_host / fin_len_host
+ * (nullable, [n]) receive the return and length of each env's LAST finished episode. */
+int cf_episode_stats(cf_env* env, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host);
+
+/* ---- pinned host memory for the host-pointer API (so its copies are asynchronous DMA) ------- */
+void* cf_host_alloc(uint64_t bytes);     /* NULL on failure (cf_last_error) */
+void cf_host_free(void* p);
+
 /* number of kernels this library has launched on this handle since creation */
 int64_t cf_launch_count(const cf_env* env);
 /* average device time (ms) of the step kernel launches since the last call with reset!=0,

@@ -400,7 +400,9 @@ void cfo_reset(cfo_env* e, const cf_config* cfg, const double* nz_in, const doub
     /* task_specific_reset, hover_free.py:237-289 / hover.py:1463-1513 */
     double pos[3] = {0, 0, 1}, rpy[3] = {0, 0, 0}, vel[3] = {0, 0, 0}, rate[3] = {0, 0, 0};
     if (cfg->enable_reset_distribution) {
-        for (int i = 0; i < 3; ++i) pos[i] += unif(-cfg->init_pos_lim, cfg->init_pos_lim, un[i]);
+        /* init_xyz is a float32 array and `pos += uniform(...)` adds in place (hover_free.py:245-251):
+         * the float64 sum is rounded to float32 */
+        for (int i = 0; i < 3; ++i) pos[i] = (double)(float)(pos[i] + unif(-cfg->init_pos_lim, cfg->init_pos_lim, un[i]));
         for (int i = 0; i < 3; ++i) rpy[i] = unif(-cfg->init_angle, cfg->init_angle, un[3 + i]);
         rpy[2] = unif(-cfg->init_yaw, cfg->init_yaw, un[6]);
         for (int i = 0; i < 3; ++i) vel[i] = vel[i] + unif(-cfg->init_vel_lim, cfg->init_vel_lim, un[7 + i]);
@@ -787,5 +789,31 @@ void cfo_gae(const float* rew, const float* val, const uint8_t* done, const floa
             disc_ret[k] = (float)run_ret;
             next_val = val[k];
         }
+    }
+}
+
+/* ------------------------------------------------------------------ HJ batch helpers (tests) */
+void cfo_hj_index_batch(const double* states, int n, int* idx) {
+    for (int i = 0; i < n; ++i) cfo_hj_index(states + 6 * (size_t)i, idx + 6 * (size_t)i);
+}
+void cfo_hj_signbits_batch(const float* V, const int* idx, int n, int* bits) {
+    for (int i = 0; i < n; ++i) bits[i] = cfo_hj_signbits(V, idx + 6 * (size_t)i);
+}
+/* packed 2-bit sign table of a whole value table: cell c -> bits (c&3)*2 of byte c>>2 */
+void cfo_hj_signs_all(const float* V, uint8_t* out) {
+    init_static();
+    long n_bytes = (CF_HJ_CELLS + 3) / 4;
+    memset(out, 0, (size_t)n_bytes);
+#pragma omp parallel for schedule(static)
+    for (long b = 0; b < n_bytes; ++b) {
+        unsigned v = 0;
+        for (int j = 0; j < 4; ++j) {
+            long c = 4 * b + j;
+            if (c >= CF_HJ_CELLS) break;
+            int idx[6]; long r = c;
+            for (int d = 5; d >= 0; --d) { idx[d] = (int)(r % 15); r /= 15; }
+            v |= (unsigned)cfo_hj_signbits(V, idx) << (2 * j);
+        }
+        out[b] = (uint8_t)v;
     }
 }

@@ -167,27 +167,48 @@ def table_dir(tables: dict):
             os.chdir(old)
 
 
-class DrawRecorder:
-    """Wraps the global np.random entry points the env stack uses and logs every draw in
-    order as (kind, ndarray).  The stream itself is untouched (MT19937 order preserved)."""
-
-    NAMES = ('normal', 'uniform', 'randn', 'choice')
+class StdDrawRecorder:
+    """Replaces the global np.random entry points the env stack uses (normal, uniform, randn,
+    choice) by wrappers that draw the STANDARD variate from the same legacy MT19937 stream and
+    apply NumPy's own affine formula (legacy_normal: loc + scale*gauss; legacy uniform:
+    low + (high-low)*double; legacy choice(p=): cdf.searchsorted(random_sample(), 'right')).
+    Results and stream order are bit-identical to the unwrapped calls (checked by
+    tests/test_oracle_reference.py); the log holds (kind, standard draws) in call order."""
 
     def __init__(self):
         self.log = []
         self._orig = {}
 
+    def _normal(self, loc=0.0, scale=1.0, size=None):
+        z = np.random.standard_normal(size)
+        self.log.append(('normal', np.array(z, dtype=np.float64).reshape(-1)))
+        return loc + scale * z
+
+    def _randn(self, *shape):
+        z = np.random.standard_normal(shape if shape else None)
+        self.log.append(('normal', np.array(z, dtype=np.float64).reshape(-1)))
+        return z
+
+    def _uniform(self, low=0.0, high=1.0, size=None):
+        if size is None:
+            size = np.broadcast(np.asarray(low), np.asarray(high)).shape or None
+        u = np.random.random_sample(size)
+        self.log.append(('uniform', np.array(u, dtype=np.float64).reshape(-1)))
+        return low + (np.asarray(high) - np.asarray(low)) * u
+
+    def _choice(self, a, size=None, replace=True, p=None):
+        assert size is None and p is not None
+        a = np.asarray(a)
+        cdf = np.asarray(p, dtype=np.float64).cumsum()
+        cdf /= cdf[-1]
+        u = np.random.random_sample()
+        self.log.append(('choice', np.array([u], dtype=np.float64)))
+        return a[cdf.searchsorted(u, side='right')]
+
     def __enter__(self):
-        for name in self.NAMES:
-            orig = getattr(np.random, name)
-            self._orig[name] = orig
-
-            def wrapped(*a, __orig=orig, __name=name, **k):
-                out = __orig(*a, **k)
-                self.log.append((__name, np.array(out, dtype=np.float64, copy=True).reshape(-1)))
-                return out
-
-            setattr(np.random, name, wrapped)
+        for name in ('normal', 'uniform', 'randn', 'choice'):
+            self._orig[name] = getattr(np.random, name)
+            setattr(np.random, name, getattr(self, '_' + name))
         return self
 
     def __exit__(self, *exc):
