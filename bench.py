@@ -1,0 +1,309 @@
+"""bench.py - env-steps/s of the HJ-adversary hover env (BASELINE.json metric) on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (CUDA, C ABI)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference algorithm on the host cores
+
+A "step" is one control step (env.step) of one shard of `--envs` envs (default 65 536 per GPU,
+BASELINE.json configs[2]: DroneHoverBulletFreeEnvWithRandomHJAdversary-v0).  To keep every timed
+step HBM-cold, each rank round-robins over `--shards` independent shards whose combined state +
+I/O exceeds the 126 MB L2, so a shard's data has been evicted when its turn comes again.
+One JSON line is printed by rank 0 (see DESIGN.md "measurement" for every key).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENV_ID = 'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0'
+HOVER = 2.0 / 1.8 - 1.0
+# ALGORITHMIC bytes per env-step (DESIGN.md "roofline"): state 216 B in +
+# 216 B out, DR params 56 B in, action 16 B in, obs 136 B + reward 4 B + done 1 B + cost 4 B out,
+# HJ packed sign table 1 B gathered.
+BYTES_PER_ENV_STEP = 216 + 216 + 56 + 16 + 136 + 4 + 1 + 4 + 1
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=2000)
+    ap.add_argument('--warmup', type=int, default=200)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--envs', type=int, default=65536, help='envs per GPU per step')
+    ap.add_argument('--shards', type=int, default=8, help='independent env shards per GPU (L2 eviction)')
+    ap.add_argument('--kfuse', type=int, default=32, help='control steps per launch in the fused side measurement')
+    ap.add_argument('--e2e-steps', type=int, default=100)
+    ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--id={index}', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                          '-lms', '100'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float) -> dict:
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for _, r in self.rows]
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in rows:
+            f = [x.strip() for x in r.split(',')]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'MEASURED_PEAKS.json hbm_gbs (of measured)'
+    return 6650.0, 'fallback 6.65 TB/s of B200_PROFILING.md (of fallback)'
+
+
+def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float):
+    """The reference algorithm on the host cores: oracle-B (float64 C restatement of the reference's
+    Python + restated Bullet step, OpenMP over envs) on a bounded sample of the same workload."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import cf_oracle as co
+    from disturbance_crazyfile_simulation_b200 import abi, hj_tables
+    cfg = abi.config_default(ENV_ID)
+    V = hj_tables.synthetic_table(1.5, 15)
+    for li in range(1, 21):          # one table shared by all levels: the lookup cost does not depend on its values
+        co.set_table(li, V)
+    orc = co.OracleEnvs(cfg, envs, seed=1)
+    orc.reset()
+    rng = np.random.default_rng(0)
+    act = (HOVER + 0.05 * rng.standard_normal((envs, 4)))
+    for _ in range(warmup):
+        orc.step(act)
+    t0 = time.perf_counter()
+    done_steps = 0
+    for _ in range(steps):
+        orc.step(act)
+        done_steps += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    dt = time.perf_counter() - t0
+    return envs * done_steps / dt, co.lib().cfo_num_threads(), done_steps, dt
+
+
+def main_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    envs = 16384
+    steps = max(1, min(args.steps, 2000))
+    value, cores, done_steps, dt = cpu_reference_run(envs, steps, min(args.warmup, 5), 60.0)
+    sample = f'{envs} envs x {done_steps} control steps of {ENV_ID} (noise, DR, auto-reset on), synthetic HJ table'
+    line = {
+        'impl': 'reference', 'metric': 'env-steps/sec (HJ-adversary hover)', 'value': value, 'unit': 'env-steps/s',
+        'n_gpus': args.gpus, 'steps': done_steps, 'warmup': min(args.warmup, 5), 'ms_per_step': 1e3 * dt / done_steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': f'{ENV_ID}, bounded CPU sample of {envs} envs per step', 'envs_per_step': envs},
+        'cpu_baseline': {'value': value, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample,
+                         'note': 'the reference itself (pure Python + PyBullet 3.21) cannot be installed here; this is its '
+                                 'algorithm restated in C (oracle-B), which is far faster than the reference\'s own '
+                                 '~1.2e3 (no adversary) / ~1.5e2 (HJ) steps/s per process (BASELINE.md)'},
+        'e2e': {'value': value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line))
+
+
+def main_ours(args):
+    import torch
+    import torch.distributed as dist
+    from disturbance_crazyfile_simulation_b200 import abi, hj_tables, make
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device - the product path has no CPU fallback')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    L = abi.lib()
+    n, S, K, W = args.envs, args.shards, args.steps, max(args.warmup, 3)
+    shards = []
+    for s in range(S):
+        # global env ids: rank-major, then shard, so results do not depend on the number of GPUs;
+        # one HJ table set per GPU, shared by its shards
+        env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=(rank * S + s) * n,
+                   share_tables_with=shards[0] if shards else None)
+        shards.append(env)
+    od = shards[0].obs_dim
+    g = torch.Generator(device=dev).manual_seed(1 + rank)
+    acts = [(HOVER + 0.05 * torch.randn((n, 4), device=dev, generator=g)).contiguous() for _ in range(S)]
+    obs = [torch.empty((n, od), device=dev) for _ in range(S)]
+    rew = [torch.empty(n, device=dev) for _ in range(S)]
+    done = [torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(S)]
+    cost = [torch.empty(n, device=dev) for _ in range(S)]
+    P = lambda t: C.c_void_p(t.data_ptr())
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    argv = [(e._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, stream) for i, e in enumerate(shards)]
+    for e in shards:
+        e.reset()
+
+    def run(k_steps, offset=0):
+        for t in range(k_steps):
+            rc = L.cf_step_dev(*argv[(offset + t) % S])
+            if rc:
+                abi.check(rc)
+
+    # ---- warm-up, then the timed region: exactly K steps between barrier + synchronize ----------
+    run(W)
+    launches0 = sum(e.launch_count for e in shards)
+    for e in shards:
+        e.kernel_timing(True, reset=True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.time()
+    ev0.record()
+    run(K, offset=W)
+    ev1.record()
+    barrier()
+    t1 = time.time()
+    ms = ev0.elapsed_time(ev1)
+    kt = [e.kernel_timing(False) for e in shards]
+    launches = sum(e.launch_count for e in shards) - launches0
+    clocks = sampler.stop(t0, t1) if sampler else None
+    kern_ms = sum(m * c for m, c in kt) / max(1, sum(c for _, c in kt))
+    t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_max = float(t_ms.item())
+    value = n * K * world / (ms_max * 1e-3)
+
+    # ---- side measurements (rank 0 only reports them) ---------------------------------------------
+    # (a) L2-resident back-to-back stepping of ONE shard; (b) K control steps fused in one launch
+    side = {}
+    e0 = shards[0]
+    ev0.record(); [L.cf_step_dev(*argv[0]) for _ in range(200)]; ev1.record(); torch.cuda.synchronize()
+    side['one_shard_l2_resident_env_steps_per_s'] = n * 200 / (ev0.elapsed_time(ev1) * 1e-3)
+    kf = args.kfuse
+    actk = (HOVER + 0.05 * torch.randn((kf, n, 4), device=dev, generator=g)).contiguous()
+    obsk = torch.empty((kf, n, od), device=dev); rewk = torch.empty((kf, n), device=dev)
+    donek = torch.empty((kf, n), dtype=torch.uint8, device=dev); costk = torch.empty((kf, n), device=dev)
+    e0.step_k(actk, obsk, rewk, donek, costk)
+    ev0.record()
+    for _ in range(5):
+        e0.step_k(actk, obsk, rewk, donek, costk)
+    ev1.record(); torch.cuda.synchronize()
+    side[f'fused_k{kf}_env_steps_per_s'] = n * kf * 5 / (ev0.elapsed_time(ev1) * 1e-3)
+    stats = e0.episode_stats()
+    side['mean_episode_length_shard0'] = stats['mean_length']
+
+    # ---- e2e: the public host-pointer API (cf_step_host) with pinned HOST buffers ---------------
+    def pinned(shape, dtype):
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        ptr = L.cf_host_alloc(nbytes)
+        assert ptr, L.cf_last_error()
+        return np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(ptr)).view(dtype).reshape(shape), ptr
+    (h_act, p0), (h_obs, p1), (h_rew, p2), (h_done, p3), (h_cost, p4) = (
+        pinned((n, 4), np.float32), pinned((n, od), np.float32), pinned((n,), np.float32), pinned((n,), np.uint8),
+        pinned((n,), np.float32))
+    h_act[:] = acts[0].cpu().numpy()
+    ke = max(3, min(args.e2e_steps, K))
+    for i in range(3):
+        shards[i % S].step_host(h_act, h_obs, h_rew, h_done, h_cost)
+    barrier()
+    te0 = time.perf_counter()
+    for i in range(ke):
+        shards[i % S].step_host(h_act, h_obs, h_rew, h_done, h_cost)   # returns with results in host memory
+    barrier()
+    te = time.perf_counter() - te0
+    t_e = torch.tensor([te], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+    e2e_value = n * ke * world / float(t_e.item())
+    for p in (p0, p1, p2, p3, p4):
+        L.cf_host_free(p)
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        achieved = BYTES_PER_ENV_STEP * n / (kern_ms * 1e-3) / 1e9
+        line = {
+            'metric': 'env-steps/sec (HJ-adversary hover)', 'value': value, 'unit': 'env-steps/s', 'n_gpus': world,
+            'steps': K, 'warmup': W, 'ms_per_step': ms_max / K, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'{ENV_ID}, {n} envs/GPU per step (BASELINE.json configs[2]); sensor noise, 10% domain '
+                                   'randomisation, Boltzmann HJ level, in-kernel auto-reset, TimeLimit 500 all on',
+                       'envs_per_gpu_per_step': n, 'shards_per_gpu': S,
+                       'l2': f'inputs larger than L2: round-robin over {S} shards, {S * n * (304 + 16 + 4 * od + 9) / 1e6:.0f} MB '
+                             'of state + I/O per GPU vs 126 MB L2', 'actions': 'hover + 0.05*N(0,1), resident in HBM',
+                       'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
+                                    'packed 2-bit sign tables in HBM/L2', 'step_mode': 'one launch per control step'},
+            'clocks': clocks, 'gpu_launches': int(launches),
+            'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
+                    'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,
+                    'api': 'cf_step_host (C ABI, pinned host buffers; copies inside the timed region)'},
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                         'traffic': None, 'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
+                         'bytes_per_env_step': BYTES_PER_ENV_STEP, 'peak_source': peak_src,
+                         'note': 'CUDA events per launch on the launching stream inside the timed region'},
+            'side': side,
+        }
+        if not args.no_cpu_baseline:
+            v, cores, steps_done, dt = cpu_reference_run(8192, 10000, 2, args.cpu_seconds)
+            line['cpu_baseline'] = {'value': v, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port',
+                                    'sample': f'8192 envs x {steps_done} control steps of the same workload ({dt:.1f} s), '
+                                              'oracle-B float64 C restatement, OpenMP'}
+        print(json.dumps(line))
+    for e in shards:
+        e.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        main_reference(a)
+    else:
+        main_ours(a)

@@ -72,6 +72,7 @@ _SIGS = {
     'cf_obs_dim': (C.c_int, [_P]),
     'cf_num_envs': (C.c_int, [_P]),
     'cf_load_hj_table': (C.c_int, [_P, C.c_int32, _P]),
+    'cf_share_hj_tables': (C.c_int, [_P, _P]),
     'cf_get_hj_signs': (C.c_int, [_P, C.c_int32, _P]),
     'cf_reset_dev': (C.c_int, [_P, _P, _P, _P]),
     'cf_step_dev': (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P]),

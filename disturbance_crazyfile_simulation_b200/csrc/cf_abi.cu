@@ -54,6 +54,7 @@ struct cf_env {
     cudaStream_t hstream = nullptr;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_cost = nullptr, *d_term = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
+    bool tables_borrowed = false;    // value_dev / signs_dev belong to another handle (cf_share_hj_tables)
     long long launches = 0;
     bool timing = false;
     std::vector<EventPair> ev_pool;
@@ -309,7 +310,8 @@ int cf_destroy(cf_env* e) {
     if (!e) return CF_OK;
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
-    for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
+    if (!e->tables_borrowed)
+        for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
     for (int i = 0; i < 4; ++i) cudaFree(e->inj[i]);
     cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
     cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
@@ -326,6 +328,7 @@ int64_t cf_launch_count(const cf_env* e) { return e ? e->launches : 0; }
 
 int cf_load_hj_table(cf_env* e, int32_t li, const float* V_host) {
     if (!e || !V_host || li < 0 || li >= CF_MAX_LEVELS) return fail(CF_ERR_INVALID, "cf_load_hj_table: bad argument%s", "");
+    if (e->tables_borrowed) return fail(CF_ERR_INVALID, "cf_load_hj_table: this handle borrows its tables (cf_share_hj_tables)%s", "");
     CU(cudaSetDevice(e->device));
     const size_t vbytes = sizeof(float) * (size_t)CF_HJ_CELLS, pbytes = (CF_HJ_CELLS + 3) / 4;
     float* V = e->value_dev[li];
@@ -339,6 +342,20 @@ int cf_load_hj_table(cf_env* e, int32_t li, const float* V_host) {
     if (e->cfg.hj_mode == CF_HJ_SIGN_TABLE) { cudaFree(V); V = nullptr; }   // 2.85 MB/level stays, 45.6 MB/level goes
     e->value_dev[li] = V;
     e->tab.value[li] = V; e->tab.signs[li] = e->signs_dev[li];
+    return CF_OK;
+}
+
+int cf_share_hj_tables(cf_env* e, const cf_env* owner) {
+    if (!e || !owner || e == owner) return fail(CF_ERR_INVALID, "cf_share_hj_tables: bad argument%s", "");
+    if (e->device != owner->device || e->cfg.hj_mode != owner->cfg.hj_mode)
+        return fail(CF_ERR_INVALID, "cf_share_hj_tables: handles must be on the same device with the same hj_mode%s", "");
+    if (!e->tables_borrowed)
+        for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
+    for (int i = 0; i < CF_MAX_LEVELS; ++i) {
+        e->value_dev[i] = owner->value_dev[i]; e->signs_dev[i] = owner->signs_dev[i];
+        e->tab.value[i] = owner->value_dev[i]; e->tab.signs[i] = owner->signs_dev[i];
+    }
+    e->tables_borrowed = true;
     return CF_OK;
 }
 

@@ -79,7 +79,7 @@ class CrazyFlieVecEnv:
 
     def __init__(self, env_id: str, num_envs: int = 1, device: Optional[int] = None, seed: int = 0,
                  env_id_base: int = 0, hj_table_dir: Optional[str] = None, hj_table_seed: int = 15,
-                 return_terminal_obs: bool = False, **kwargs):
+                 return_terminal_obs: bool = False, share_tables_with: Optional['CrazyFlieVecEnv'] = None, **kwargs):
         L = abi.lib()
         if not torch.cuda.is_available():
             raise RuntimeError('CrazyFlieVecEnv needs a CUDA device (no CPU fallback)')
@@ -113,7 +113,11 @@ class CrazyFlieVecEnv:
         self._cost = torch.empty((n,), dtype=torch.float32, device=self.device)
         self._trunc = torch.empty((n,), dtype=torch.uint8, device=self.device)
         self._term = torch.zeros((n, od), dtype=torch.float32, device=self.device) if return_terminal_obs else None
-        self._load_tables(hj_table_dir, hj_table_seed)
+        self._table_owner = share_tables_with        # keeps the owner alive
+        if share_tables_with is not None:
+            abi.check(L.cf_share_hj_tables(self._h, share_tables_with._h))
+        else:
+            self._load_tables(hj_table_dir, hj_table_seed)
 
     # ------------------------------------------------------------------ tables
     def _needed_levels(self):

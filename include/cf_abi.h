@@ -141,6 +141,9 @@ int cf_num_envs(const cf_env* env);
 /* np.load(fastrack_{level}_15x15.npy) of distur_gener.py:155, hoisted: upload one float32
  * (15,)*6 C-order value table (HOST pointer) for level index round(level*10). */
 int cf_load_hj_table(cf_env* env, int32_t level_idx, const float* V_host);
+/* Let `env` use the device tables already uploaded to `owner` (same device, same hj_mode) instead of
+ * its own copy: one table set per GPU shared by all env shards.  `owner` must outlive `env`. */
+int cf_share_hj_tables(cf_env* env, const cf_env* owner);
 /* read back the packed 2-bit sign table of a level (HOST pointer, CF_HJ_CELLS/4+1 bytes) */
 int cf_get_hj_signs(cf_env* env, int32_t level_idx, uint8_t* out_host);
 
