@@ -32,6 +32,8 @@ HOVER = 2.0 / 1.8 - 1.0
 # 216 B out, DR params 56 B in, action 16 B in, obs 136 B + reward 4 B + done 1 B + cost 4 B out,
 # HJ packed sign table 1 B gathered.
 BYTES_PER_ENV_STEP = 216 + 216 + 56 + 16 + 136 + 4 + 1 + 4 + 1
+# dram__bytes_read.sum + dram__bytes_write.sum per k_step launch, from the committed ncu capture (None until measured)
+TRAFFIC_NCU = None
 
 
 def parse():
@@ -46,6 +48,7 @@ def parse():
     ap.add_argument('--e2e-steps', type=int, default=100)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
 
@@ -184,36 +187,62 @@ def main_ours(args):
     done = [torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(S)]
     cost = [torch.empty(n, device=dev) for _ in range(S)]
     P = lambda t: C.c_void_p(t.data_ptr())
-    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    argv = [(e._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, stream) for i, e in enumerate(shards)]
+
+    def step_shard(i):
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        rc = L.cf_step_dev(shards[i]._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, stream)
+        if rc:
+            abi.check(rc)
+
     for e in shards:
         e.reset()
 
     def run(k_steps, offset=0):
         for t in range(k_steps):
-            rc = L.cf_step_dev(*argv[(offset + t) % S])
-            if rc:
-                abi.check(rc)
+            step_shard((offset + t) % S)
 
-    # ---- warm-up, then the timed region: exactly K steps between barrier + synchronize ----------
+    # ---- warm-up (direct launches), then one CUDA graph of S launches (one control step of every shard) --
     run(W)
-    launches0 = sum(e.launch_count for e in shards)
+    torch.cuda.synchronize()
+    graph = None
+    if not args.no_graph:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            run(S, offset=W)
+        graph.replay()                                   # untimed warm-up replay
+        torch.cuda.synchronize()
+
+    def run_timed(k_steps):
+        """exactly k_steps control steps: whole-graph replays (S steps each) + direct launches for the rest"""
+        if graph is None:
+            run(k_steps, offset=W)
+            return
+        for _ in range(k_steps // S):
+            graph.replay()
+        run(k_steps % S, offset=W)
+
+    # per-launch device time of the step kernel with CUDA events on the launching stream (direct launches)
     for e in shards:
         e.kernel_timing(True, reset=True)
+    run(min(K, 200), offset=W)
+    torch.cuda.synchronize()
+    kt = [e.kernel_timing(False) for e in shards]
+    kern_ms_events = sum(m * c for m, c in kt) / max(1, sum(c for _, c in kt))
+
+    # ---- the timed region: exactly K steps between barrier + synchronize -----------------------------
     sampler = ClockSampler(local) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t0 = time.time()
     ev0.record()
-    run(K, offset=W)
+    run_timed(K)
     ev1.record()
     barrier()
     t1 = time.time()
     ms = ev0.elapsed_time(ev1)
-    kt = [e.kernel_timing(False) for e in shards]
-    launches = sum(e.launch_count for e in shards) - launches0
+    launches = K                                         # one k_step launch per control step (graph nodes included)
     clocks = sampler.stop(t0, t1) if sampler else None
-    kern_ms = sum(m * c for m, c in kt) / max(1, sum(c for _, c in kt))
+    kern_ms = ms / K                                     # launch-to-launch time of the dominant kernel inside the timed region
     t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
@@ -224,7 +253,7 @@ def main_ours(args):
     # (a) L2-resident back-to-back stepping of ONE shard; (b) K control steps fused in one launch
     side = {}
     e0 = shards[0]
-    ev0.record(); [L.cf_step_dev(*argv[0]) for _ in range(200)]; ev1.record(); torch.cuda.synchronize()
+    ev0.record(); [step_shard(0) for _ in range(200)]; ev1.record(); torch.cuda.synchronize()
     side['one_shard_l2_resident_env_steps_per_s'] = n * 200 / (ev0.elapsed_time(ev1) * 1e-3)
     kf = args.kfuse
     actk = (HOVER + 0.05 * torch.randn((kf, n, 4), device=dev, generator=g)).contiguous()
@@ -278,15 +307,19 @@ def main_ours(args):
                        'l2': f'inputs larger than L2: round-robin over {S} shards, {S * n * (304 + 16 + 4 * od + 9) / 1e6:.0f} MB '
                              'of state + I/O per GPU vs 126 MB L2', 'actions': 'hover + 0.05*N(0,1), resident in HBM',
                        'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
-                                    'packed 2-bit sign tables in HBM/L2', 'step_mode': 'one launch per control step'},
+                                    'packed 2-bit sign tables in HBM/L2',
+                       'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S} (one per shard)')},
             'clocks': clocks, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
                     'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,
                     'api': 'cf_step_host (C ABI, pinned host buffers; copies inside the timed region)'},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': None, 'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
+                         'traffic': TRAFFIC_NCU, 'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
+                         'avg_kernel_ms_events_per_launch': kern_ms_events,
                          'bytes_per_env_step': BYTES_PER_ENV_STEP, 'peak_source': peak_src,
-                         'note': 'CUDA events per launch on the launching stream inside the timed region'},
+                         'note': 'avg_kernel_ms = CUDA-event time of the timed region / launches in it (launch gaps included); '
+                                 'avg_kernel_ms_events_per_launch = CUDA events around each direct launch on the launching stream; '
+                                 'traffic = dram bytes per launch from the committed ncu --set full capture (profiles/)'},
             'side': side,
         }
         if not args.no_cpu_baseline:

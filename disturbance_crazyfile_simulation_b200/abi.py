@@ -84,9 +84,12 @@ _SIGS = {
     'cf_get_levels': (C.c_int, [_P, _P]),
     'cf_set_noise_override': (C.c_int, [_P, _P, _P, _P, _P]),
     'cf_hj_lookup_host': (C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, _P]),
+    'cf_hj_lookup_f32_host': (C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, _P]),
     'cf_episode_stats': (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     'cf_gae_dev': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P, _P]),
     'cf_gae_host': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P]),
+    'cf_set_trace_buffer': (C.c_int, [_P, _P]),
+    'cf_num_tiles': (C.c_int, [_P]),
     'cf_launch_count': (C.c_int64, [_P]),
     'cf_kernel_timing': (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'cf_host_alloc': (_P, [C.c_uint64]),

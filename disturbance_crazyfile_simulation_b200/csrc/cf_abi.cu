@@ -41,21 +41,26 @@ struct cf_env {
     cf_config cfg;
     DevCfg dev;
     DevTables tab;
-    int n = 0, device = 0, obs_dim = 34;
-    float4* S = nullptr;
-    float* value_dev[CF_MAX_LEVELS] = {};
-    uint8_t* signs_dev[CF_MAX_LEVELS] = {};
+    int n = 0, n_pad = 0, device = 0, obs_dim = 34;
+    float* S = nullptr;                          // [n_pad / CF_TILE][CF_STATE_WORDS][CF_TILE]
+    float* value_dev[CF_MAX_LEVELS] = {};        // host copy of the device pointer array tab.value
+    bool has_signs[CF_MAX_LEVELS] = {};
+    const float** value_ptrs_dev = nullptr;      // device array [CF_MAX_LEVELS]
+    uint8_t* signs_slab = nullptr;               // [CF_MAX_LEVELS][CF_SIGN_STRIDE]
+    float* thr_dev = nullptr;                    // [6][16]
+    const cf_env* table_owner = nullptr;
     float* inj[4] = {};              // step z, step u, reset z, reset u
     float* fin_ret = nullptr;
     int* fin_len = nullptr;
     double* agg = nullptr;
-    float4* rec_dev = nullptr;       // scratch for get/set_state
+    float* rec_dev = nullptr;        // scratch for get/set_state
     // host-pointer API: private stream + device mirrors of the caller's host buffers
     cudaStream_t hstream = nullptr;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_cost = nullptr, *d_term = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
-    bool tables_borrowed = false;    // value_dev / signs_dev belong to another handle (cf_share_hj_tables)
+    bool tables_borrowed = false;    // tables belong to another handle (cf_share_hj_tables)
     long long launches = 0;
+    unsigned long long* trace = nullptr;   // caller-owned device buffer (cf_set_trace_buffer)
     bool timing = false;
     std::vector<EventPair> ev_pool;
     size_t ev_used = 0;
@@ -112,6 +117,34 @@ void grid_tables(double grid[6][CF_HJ_PTS], double dx[6], double cdf[21]) {
     for (int k = 0; k < 21; ++k) cdf[k] /= last;
 }
 
+// Grid.get_index (odp/Grid/GridProcessing.py:53-72) in float64, as hj_index_dim on the device
+int index_f64(const double* g, double s) {
+    if (!(s == s)) return CF_HJ_PTS - 1;
+    int i = 0;
+    while (i < 15 && g[i] < s) ++i;                      /* np.searchsorted(side='left') */
+    if (i > 0 && (i == 15 || fabs(s - g[i - 1]) < fabs(s - g[i]))) i -= 1;
+    return i;
+}
+// float32 <-> order-preserving integer
+int64_t f2ord(float f) { int32_t b; memcpy(&b, &f, 4); return b >= 0 ? (int64_t)b : -(int64_t)(b & 0x7fffffff); }
+float ord2f(int64_t o) { int32_t b = o >= 0 ? (int32_t)o : (int32_t)((uint32_t)(-o) | 0x80000000u); float f; memcpy(&f, &b, 4); return f; }
+// thr[d][j] = smallest float32 whose float64-rule index is >= j+1 (the rule is monotone in s), found
+// by bisection over the float32 values between grid points j and j+1; slots 14, 15 = NaN (never true)
+void index_thresholds(const double grid[6][CF_HJ_PTS], float thr[6][16]) {
+    for (int d = 0; d < 6; ++d) {
+        for (int j = 0; j < 14; ++j) {
+            int64_t lo = f2ord(nextafterf((float)grid[d][j], -INFINITY));       /* index <= j */
+            int64_t hi = f2ord(nextafterf((float)grid[d][j + 1], INFINITY));    /* index >= j+1 */
+            while (hi - lo > 1) {
+                int64_t mid = lo + (hi - lo) / 2;
+                if (index_f64(grid[d], (double)ord2f(mid)) >= j + 1) hi = mid; else lo = mid;
+            }
+            thr[d][j] = ord2f(hi);
+        }
+        thr[d][14] = thr[d][15] = NAN;
+    }
+}
+
 int derive(const cf_config& c, uint64_t seed, int64_t gid_base, DevCfg& d) {
     if (c.abi_version != CF_ABI_VERSION) return fail(CF_ERR_INVALID, "cf_config.abi_version mismatch%s (got %lld)", "", c.abi_version);
     if (c.aggregate_phy_steps != 2) return fail(CF_ERR_INVALID, "aggregate_phy_steps must be 2%s (got %lld)", "", c.aggregate_phy_steps);
@@ -165,7 +198,20 @@ int derive(const cf_config& c, uint64_t seed, int64_t gid_base, DevCfg& d) {
         double max_thrust = (G * M) * T2W / 4.0, max_rpm = sqrt((T2W * (G * M)) / (4.0 * max_thrust));
         d.gnd_hclip = (float)(0.25 * pr * sqrt((15.0 * max_rpm * max_rpm * kf * gnd) / max_thrust));
     }
-    d.seed_lo = (uint32_t)seed; d.seed_hi = (uint32_t)(seed >> 32);
+    {   // Philox4x32-10 key schedule of the seed (constant-bank operands in the kernels)
+        uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+        for (int r = 0; r < 10; ++r) { d.pk[r][0] = k0; d.pk[r][1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    }
+    {
+        double grid[6][CF_HJ_PTS], dx[6], cdf[21];
+        grid_tables(grid, dx, cdf);
+        for (int k = 0; k < 6; ++k) { d.hj_lo[k] = (float)grid[k][0]; d.hj_inv_dx[k] = (float)(1.0 / dx[k]); }
+        for (int k = 0; k < 20; ++k) {                      // smallest float32 t with cdf[k] <= (double)t
+            float t = (float)cdf[k];
+            if ((double)t < cdf[k]) t = nextafterf(t, INFINITY);
+            d.boltz_thr[k] = t;
+        }
+    }
     d.gid_base = gid_base;
     return CF_OK;
 }
@@ -196,7 +242,8 @@ void drain_timing(cf_env* e) {
 
 int check_tables(cf_env* e) {
     const cf_config& c = e->cfg;
-    auto have = [&](int li) { return c.hj_mode == CF_HJ_SIGN_TABLE ? e->signs_dev[li] != nullptr : e->value_dev[li] != nullptr; };
+    const cf_env* o = e->tables_borrowed ? e->table_owner : e;
+    auto have = [&](int li) { return c.hj_mode == CF_HJ_SIGN_TABLE ? o->has_signs[li] : o->value_dev[li] != nullptr; };
     if (c.disturbance_kind == CF_DSTB_HJ_FIXED) {
         int li = e->dev.fixed_level_idx;
         if (li > 0 && !have(li)) return fail(CF_ERR_NO_TABLE, "no HJ value table loaded for level index %s%lld", "", li);
@@ -220,10 +267,17 @@ int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint
     io.term_obs = term_obs; io.truncated = truncated;
     io.inj_step_z = e->inj[0]; io.inj_step_u = e->inj[1]; io.inj_reset_z = e->inj[2]; io.inj_reset_u = e->inj[3];
     io.fin_ret = e->fin_ret; io.fin_len = e->fin_len; io.agg = e->agg;
+    // a full tile's observation rows leave with one bulk copy when every tile's first row is 16-byte aligned
+    io.trace = e->trace;
+    io.bulk_obs = ((uintptr_t)obs % 16 == 0) && (k == 1 || ((size_t)e->n * e->obs_dim * 4) % 16 == 0);
+    if ((uintptr_t)act % 16 != 0) return fail(CF_ERR_INVALID, "cf_step: act must be 16-byte aligned%s", "");
+    if ((uintptr_t)obs % 8 != 0 || (term_obs && (uintptr_t)term_obs % 8 != 0))
+        return fail(CF_ERR_INVALID, "cf_step: obs rows must be 8-byte aligned%s", "");
     EventPair* ep;
     begin_timing(e, st, &ep);
-    launch_step(e->S, e->n, k, e->dev, e->tab, io, st);
+    cudaError_t lerr = launch_step(e->S, e->n, k, e->dev, e->tab, io, st);
     end_timing(ep, st);
+    if (lerr != cudaSuccess) return cuda_fail(lerr, "launch_step");
     e->launches += 1;
     CU(cudaGetLastError());
     return CF_OK;
@@ -288,20 +342,30 @@ int cf_create(const cf_config* cfg, int32_t n_envs, int32_t device, uint64_t see
     cf_env* e = new (std::nothrow) cf_env();
     if (!e) return fail(CF_ERR_ALLOC, "out of host memory%s", "");
     e->cfg = *cfg; e->dev = dev; e->n = n_envs; e->device = device; e->obs_dim = dev.obs_dim;
+    e->n_pad = (n_envs + CF_TILE - 1) / CF_TILE * CF_TILE;
     memset(&e->tab, 0, sizeof(e->tab));
     double grid[6][CF_HJ_PTS], dx[6], cdf[21];
+    float thr[6][16];
     grid_tables(grid, dx, cdf);
+    index_thresholds(grid, thr);
+    const bool hj = cfg->disturbance_kind == CF_DSTB_HJ_FIXED || cfg->disturbance_kind == CF_DSTB_HJ_BOLTZMANN;
     cudaError_t err = upload_constants(grid, dx, cdf);
-    if (err == cudaSuccess) err = cudaMalloc((void**)&e->S, sizeof(float4) * kGroups * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->S, sizeof(float) * CF_STATE_WORDS * (size_t)e->n_pad);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_ret, sizeof(float) * (size_t)n_envs);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_len, sizeof(int) * (size_t)n_envs);
-    if (err == cudaSuccess) err = cudaMalloc((void**)&e->agg, sizeof(double) * 4);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->agg, sizeof(double) * 4 * CF_AGG_SLOTS);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->thr_dev, sizeof(thr));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->value_ptrs_dev, sizeof(float*) * CF_MAX_LEVELS);
+    if (err == cudaSuccess && hj) err = cudaMalloc((void**)&e->signs_slab, (size_t)CF_SIGN_STRIDE * CF_MAX_LEVELS);
     if (err == cudaSuccess) err = cudaMemset(e->fin_ret, 0, sizeof(float) * (size_t)n_envs);
     if (err == cudaSuccess) err = cudaMemset(e->fin_len, 0, sizeof(int) * (size_t)n_envs);
-    if (err == cudaSuccess) err = cudaMemset(e->agg, 0, sizeof(double) * 4);
+    if (err == cudaSuccess) err = cudaMemset(e->agg, 0, sizeof(double) * 4 * CF_AGG_SLOTS);
+    if (err == cudaSuccess) err = cudaMemset(e->value_ptrs_dev, 0, sizeof(float*) * CF_MAX_LEVELS);
+    if (err == cudaSuccess) err = cudaMemcpy(e->thr_dev, thr, sizeof(thr), cudaMemcpyHostToDevice);
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking);
-    if (err == cudaSuccess) { launch_init(e->S, n_envs, e->dev, 0); e->launches += 1; err = cudaDeviceSynchronize(); }
+    if (err == cudaSuccess) { launch_init(e->S, e->n_pad, e->dev, 0); e->launches += 1; err = cudaDeviceSynchronize(); }
     if (err != cudaSuccess) { cuda_fail(err, "cf_create"); cf_destroy(e); return err == cudaErrorMemoryAllocation ? CF_ERR_ALLOC : CF_ERR_CUDA; }
+    e->tab.value = e->value_ptrs_dev; e->tab.signs = e->signs_slab; e->tab.thr = e->thr_dev;
     *out = e;
     return CF_OK;
 }
@@ -310,8 +374,8 @@ int cf_destroy(cf_env* e) {
     if (!e) return CF_OK;
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
-    if (!e->tables_borrowed)
-        for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
+    for (int i = 0; i < CF_MAX_LEVELS; ++i) cudaFree(e->value_dev[i]);
+    cudaFree(e->signs_slab); cudaFree((void*)e->value_ptrs_dev); cudaFree(e->thr_dev);
     for (int i = 0; i < 4; ++i) cudaFree(e->inj[i]);
     cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
     cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
@@ -330,18 +394,20 @@ int cf_load_hj_table(cf_env* e, int32_t li, const float* V_host) {
     if (!e || !V_host || li < 0 || li >= CF_MAX_LEVELS) return fail(CF_ERR_INVALID, "cf_load_hj_table: bad argument%s", "");
     if (e->tables_borrowed) return fail(CF_ERR_INVALID, "cf_load_hj_table: this handle borrows its tables (cf_share_hj_tables)%s", "");
     CU(cudaSetDevice(e->device));
-    const size_t vbytes = sizeof(float) * (size_t)CF_HJ_CELLS, pbytes = (CF_HJ_CELLS + 3) / 4;
+    const size_t vbytes = sizeof(float) * (size_t)CF_HJ_CELLS;
+    int rc = ensure(&e->signs_slab, (size_t)CF_SIGN_STRIDE * CF_MAX_LEVELS);
+    if (rc != CF_OK) return rc;
+    e->tab.signs = e->signs_slab;
     float* V = e->value_dev[li];
     if (!V) { cudaError_t err = cudaMalloc((void**)&V, vbytes); if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc(value table)"); return CF_ERR_ALLOC; } }
     CU(cudaMemcpy(V, V_host, vbytes, cudaMemcpyHostToDevice));
-    int rc = ensure(&e->signs_dev[li], pbytes);
-    if (rc != CF_OK) { if (!e->value_dev[li]) cudaFree(V); return rc; }
-    launch_hj_signs(V, e->signs_dev[li], 0);
+    launch_hj_signs(V, e->signs_slab + (size_t)li * CF_SIGN_STRIDE, 0);
     e->launches += 1;
     CU(cudaDeviceSynchronize());
     if (e->cfg.hj_mode == CF_HJ_SIGN_TABLE) { cudaFree(V); V = nullptr; }   // 2.85 MB/level stays, 45.6 MB/level goes
     e->value_dev[li] = V;
-    e->tab.value[li] = V; e->tab.signs[li] = e->signs_dev[li];
+    e->has_signs[li] = true;
+    CU(cudaMemcpy((void*)(e->value_ptrs_dev + li), &V, sizeof(float*), cudaMemcpyHostToDevice));
     return CF_OK;
 }
 
@@ -349,21 +415,23 @@ int cf_share_hj_tables(cf_env* e, const cf_env* owner) {
     if (!e || !owner || e == owner) return fail(CF_ERR_INVALID, "cf_share_hj_tables: bad argument%s", "");
     if (e->device != owner->device || e->cfg.hj_mode != owner->cfg.hj_mode)
         return fail(CF_ERR_INVALID, "cf_share_hj_tables: handles must be on the same device with the same hj_mode%s", "");
-    if (!e->tables_borrowed)
-        for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); cudaFree(e->signs_dev[i]); }
-    for (int i = 0; i < CF_MAX_LEVELS; ++i) {
-        e->value_dev[i] = owner->value_dev[i]; e->signs_dev[i] = owner->signs_dev[i];
-        e->tab.value[i] = owner->value_dev[i]; e->tab.signs[i] = owner->signs_dev[i];
-    }
+    if (owner->tables_borrowed) return fail(CF_ERR_INVALID, "cf_share_hj_tables: owner itself borrows its tables%s", "");
+    CU(cudaSetDevice(e->device));
+    // this handle's own (empty or loaded) tables are released; it reads the owner's from now on
+    for (int i = 0; i < CF_MAX_LEVELS; ++i) { cudaFree(e->value_dev[i]); e->value_dev[i] = nullptr; e->has_signs[i] = false; }
+    cudaFree(e->signs_slab); e->signs_slab = nullptr;
+    e->tab.value = owner->value_ptrs_dev; e->tab.signs = owner->signs_slab;
+    e->table_owner = owner;
     e->tables_borrowed = true;
     return CF_OK;
 }
 
 int cf_get_hj_signs(cf_env* e, int32_t li, uint8_t* out_host) {
     if (!e || !out_host || li < 0 || li >= CF_MAX_LEVELS) return fail(CF_ERR_INVALID, "cf_get_hj_signs: bad argument%s", "");
-    if (!e->signs_dev[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
+    const cf_env* o = e->tables_borrowed ? e->table_owner : e;
+    if (!o->has_signs[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
     CU(cudaSetDevice(e->device));
-    CU(cudaMemcpy(out_host, e->signs_dev[li], (CF_HJ_CELLS + 3) / 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out_host, o->signs_slab + (size_t)li * CF_SIGN_STRIDE, (CF_HJ_CELLS + 3) / 4, cudaMemcpyDeviceToHost));
     return CF_OK;
 }
 
@@ -439,22 +507,22 @@ int cf_step_host(cf_env* e, const float* act, float* obs, float* rew, uint8_t* d
 int cf_get_state(cf_env* e, float* state_host) {
     if (!e || !state_host) return fail(CF_ERR_INVALID, "cf_get_state: null argument%s", "");
     CU(cudaSetDevice(e->device));
-    int rc = ensure(&e->rec_dev, (size_t)kGroups * e->n);
+    int rc = ensure(&e->rec_dev, (size_t)CF_STATE_WORDS * e->n);
     if (rc != CF_OK) return rc;
     CU(cudaDeviceSynchronize());
     launch_unpack_state(e->S, e->n, e->rec_dev, 0);
     e->launches += 1;
-    CU(cudaMemcpy(state_host, e->rec_dev, sizeof(float4) * kGroups * (size_t)e->n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(state_host, e->rec_dev, sizeof(float) * CF_STATE_WORDS * (size_t)e->n, cudaMemcpyDeviceToHost));
     return CF_OK;
 }
 
 int cf_set_state(cf_env* e, const float* state_host) {
     if (!e || !state_host) return fail(CF_ERR_INVALID, "cf_set_state: null argument%s", "");
     CU(cudaSetDevice(e->device));
-    int rc = ensure(&e->rec_dev, (size_t)kGroups * e->n);
+    int rc = ensure(&e->rec_dev, (size_t)CF_STATE_WORDS * e->n);
     if (rc != CF_OK) return rc;
     CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(e->rec_dev, state_host, sizeof(float4) * kGroups * (size_t)e->n, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(e->rec_dev, state_host, sizeof(float) * CF_STATE_WORDS * (size_t)e->n, cudaMemcpyHostToDevice));
     launch_pack_state(e->S, e->n, e->rec_dev, 0);
     e->launches += 1;
     CU(cudaDeviceSynchronize());
@@ -488,36 +556,50 @@ int cf_set_noise_override(cf_env* e, const float* sz, const float* su, const flo
     return CF_OK;
 }
 
-int cf_hj_lookup_host(cf_env* e, int32_t li, const double* states, int32_t n, int32_t* idx, float* dstb_sign) {
+static int hj_lookup_impl(cf_env* e, int32_t li, const void* states, bool f32, int32_t n, int32_t* idx, float* dstb_sign) {
     if (!e || !states || !idx || !dstb_sign || n < 1 || li < 0 || li >= CF_MAX_LEVELS)
-        return fail(CF_ERR_INVALID, "cf_hj_lookup_host: bad argument%s", "");
+        return fail(CF_ERR_INVALID, "cf_hj_lookup: bad argument%s", "");
+    const cf_env* o = e->tables_borrowed ? e->table_owner : e;
     const bool use_value = e->cfg.hj_mode == CF_HJ_VALUE_TABLE;
-    if (use_value ? !e->value_dev[li] : !e->signs_dev[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
+    if (use_value ? !o->value_dev[li] : !o->has_signs[li]) return fail(CF_ERR_NO_TABLE, "no table for level index %s%lld", "", li);
     CU(cudaSetDevice(e->device));
-    double* ds = nullptr; int* di = nullptr; float* dd = nullptr;
-    cudaError_t err = cudaMalloc((void**)&ds, sizeof(double) * 6 * (size_t)n);
+    const size_t sbytes = (f32 ? sizeof(float) : sizeof(double)) * 6 * (size_t)n;
+    void* ds = nullptr; int* di = nullptr; float* dd = nullptr;
+    cudaError_t err = cudaMalloc(&ds, sbytes);
     if (err == cudaSuccess) err = cudaMalloc((void**)&di, sizeof(int) * 6 * (size_t)n);
     if (err == cudaSuccess) err = cudaMalloc((void**)&dd, sizeof(float) * 2 * (size_t)n);
-    if (err == cudaSuccess) err = cudaMemcpy(ds, states, sizeof(double) * 6 * (size_t)n, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMemcpy(ds, states, sbytes, cudaMemcpyHostToDevice);
     if (err == cudaSuccess) {
-        launch_hj_lookup(ds, n, use_value ? e->value_dev[li] : nullptr, use_value ? nullptr : e->signs_dev[li], di, dd, 0);
+        const float* V = use_value ? o->value_dev[li] : nullptr;
+        const uint8_t* P = use_value ? nullptr : o->signs_slab + (size_t)li * CF_SIGN_STRIDE;
+        if (f32) launch_hj_lookup_f32((const float*)ds, n, e->dev, V, P, e->thr_dev, di, dd, 0);
+        else launch_hj_lookup((const double*)ds, n, V, P, di, dd, 0);
         e->launches += 1;
         err = cudaMemcpy(idx, di, sizeof(int) * 6 * (size_t)n, cudaMemcpyDeviceToHost);
     }
     if (err == cudaSuccess) err = cudaMemcpy(dstb_sign, dd, sizeof(float) * 2 * (size_t)n, cudaMemcpyDeviceToHost);
     cudaFree(ds); cudaFree(di); cudaFree(dd);
-    if (err != cudaSuccess) return cuda_fail(err, "cf_hj_lookup_host");
+    if (err != cudaSuccess) return cuda_fail(err, "cf_hj_lookup");
     return CF_OK;
+}
+
+int cf_hj_lookup_host(cf_env* e, int32_t li, const double* states, int32_t n, int32_t* idx, float* dstb_sign) {
+    return hj_lookup_impl(e, li, states, false, n, idx, dstb_sign);
+}
+int cf_hj_lookup_f32_host(cf_env* e, int32_t li, const float* states, int32_t n, int32_t* idx, float* dstb_sign) {
+    return hj_lookup_impl(e, li, states, true, n, idx, dstb_sign);
 }
 
 int cf_episode_stats(cf_env* e, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host) {
     if (!e || !out) return fail(CF_ERR_INVALID, "cf_episode_stats: null argument%s", "");
     CU(cudaSetDevice(e->device));
     CU(cudaDeviceSynchronize());
-    CU(cudaMemcpy(out, e->agg, sizeof(double) * 4, cudaMemcpyDeviceToHost));
+    double slots[4 * CF_AGG_SLOTS];
+    CU(cudaMemcpy(slots, e->agg, sizeof(slots), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 4; ++k) { out[k] = 0.0; for (int j = 0; j < CF_AGG_SLOTS; ++j) out[k] += slots[4 * j + k]; }
     if (fin_ret_host) CU(cudaMemcpy(fin_ret_host, e->fin_ret, sizeof(float) * (size_t)e->n, cudaMemcpyDeviceToHost));
     if (fin_len_host) CU(cudaMemcpy(fin_len_host, e->fin_len, sizeof(int) * (size_t)e->n, cudaMemcpyDeviceToHost));
-    if (reset) CU(cudaMemset(e->agg, 0, sizeof(double) * 4));
+    if (reset) CU(cudaMemset(e->agg, 0, sizeof(double) * 4 * CF_AGG_SLOTS));
     return CF_OK;
 }
 
@@ -558,6 +640,13 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
     if (err != cudaSuccess) return cuda_fail(err, "cf_gae_host");
     return CF_OK;
 }
+
+int cf_set_trace_buffer(cf_env* e, uint64_t* trace_dev) {
+    if (!e) return fail(CF_ERR_INVALID, "cf_set_trace_buffer: null handle%s", "");
+    e->trace = (unsigned long long*)trace_dev;
+    return CF_OK;
+}
+int cf_num_tiles(const cf_env* e) { return e ? e->n_pad / CF_TILE : CF_ERR_INVALID; }
 
 int cf_kernel_timing(cf_env* e, int32_t enable, int32_t reset, double* avg_ms, int64_t* launches) {
     if (!e) return fail(CF_ERR_INVALID, "cf_kernel_timing: null handle%s", "");

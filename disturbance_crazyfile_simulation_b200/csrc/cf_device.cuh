@@ -1,12 +1,16 @@
 // cf_device.cuh - per-env device code of the batched CrazyFlie hover environment (sm_100a).
 //
-// One thread owns one env and keeps its whole 76-word state in registers across the control
-// step: HJ disturbance lookup, 2 physics substeps (PT1 motor lag, thrust/torque, drag,
-// disturbance torque, rigid-body integration), sensor-noise pipeline with gyro low-pass,
-// observation history, reward, done/cost, TimeLimit and the in-place auto-reset with domain
-// randomisation.  fp32 arithmetic (the reference is float64 NumPy + PyBullet); the operation
-// order follows the reference functions cited at each routine (paths relative to
-// phoenix_drone_simulation/ of the reference checkout).
+// One thread owns one env.  The env's 76-word state record lives word-major inside a tile of
+// CF_TILE envs ([tile][word][env] floats), so the same accessor (EnvRef: base pointer + stride
+// CF_TILE) works on the tile staged in shared memory by the step kernel and on the tile in
+// global memory (reset / init kernels); consecutive threads touch consecutive floats either way.
+// The control step is written in phases that pull only the words they need into registers: HJ
+// disturbance lookup, 2 physics substeps (PT1 motor lag, thrust/torque, drag, disturbance torque,
+// rigid-body integration), sensor-noise pipeline with gyro low-pass, observation history, reward,
+// done/cost, TimeLimit, and the in-place auto-reset with domain randomisation.  Random draws are
+// produced block by block (Philox4x32-10) right before they are consumed.  fp32 arithmetic (the
+// reference is float64 NumPy + PyBullet); each routine cites the reference function it follows
+// (paths relative to phoenix_drone_simulation/ of the reference checkout).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -21,88 +25,122 @@ __constant__ double c_grid[6][CF_HJ_PTS];   // odp Grid.grid_points, float64 lin
 __constant__ double c_dx[6];
 __constant__ double c_boltz_cdf[21];
 
+// ---------------------------------------------------------------------------------- fast math
+// MUFU-based approximations (<= 2 ulp) for quantities whose error budget is 1e-5 relative.
+__device__ __forceinline__ float fsqrt(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float frcp(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(hi, fmaxf(lo, v)); }
+
 // ---------------------------------------------------------------------------------- RNG
-// Philox4x32-10, counter = (gid_lo, event counter, block, tag ^ gid_hi<<8), key = seed.
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+// Philox4x32-10, counter = (gid_lo, event counter, block, tag ^ gid_hi<<8), key = seed.  The ten
+// round keys are derived on the host (DevCfg::pk) so they are constant-bank operands here.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, const DevCfg& cfg) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
         uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        c = make_uint4(hi1 ^ c.y ^ cfg.pk[r][0], lo1, hi0 ^ c.w ^ cfg.pk[r][1], lo0);
     }
     return c;
 }
+// 23 random bits -> (2k+1) / 2^24 in (0,1): mantissa trick, no int->float conversion (XU pipe)
 __device__ __forceinline__ float u01(uint32_t w) {
-    return fmaf((float)(w >> 8), 1.0f / 16777216.0f, 0.5f / 16777216.0f);
+    return __uint_as_float(0x3f800000u | (w >> 9)) - 0.99999994f;   // 1 - 2^-24, exact
 }
 struct Rng {
-    uint32_t k0, k1, c0, c1, c3;
-    __device__ __forceinline__ uint4 raw(uint32_t block) const {
-        return philox4x32_10(make_uint4(c0, c1, block, c3), k0, k1);
+    uint32_t c0, c1, c3;
+    __device__ __forceinline__ uint4 raw(const DevCfg& cfg, uint32_t block) const {
+        return philox4x32_10(make_uint4(c0, c1, block, c3), cfg);
     }
     // four standard normals of block b (Box-Muller on two pairs, same pairing as the oracle)
-    __device__ __forceinline__ float4 normals(uint32_t b) const {
-        uint4 w = raw(b);
-        float r0 = sqrtf(-2.0f * __logf(u01(w.x))), r1 = sqrtf(-2.0f * __logf(u01(w.z)));
+    __device__ __forceinline__ float4 normals(const DevCfg& cfg, uint32_t b) const {
+        uint4 w = raw(cfg, b);
+        float r0 = fsqrt(-2.0f * __logf(u01(w.x))), r1 = fsqrt(-2.0f * __logf(u01(w.z)));
         float s0, c0_, s1, c1_;
         __sincosf(kPi * (2.0f * u01(w.y) - 1.0f), &s0, &c0_);
         __sincosf(kPi * (2.0f * u01(w.w) - 1.0f), &s1, &c1_);
         return make_float4(r0 * c0_, r0 * s0, r1 * c1_, r1 * s1);
     }
-    __device__ __forceinline__ float4 uniforms(uint32_t b) const {
-        uint4 w = raw(16u + b);
+    __device__ __forceinline__ float4 uniforms(const DevCfg& cfg, uint32_t b) const {
+        uint4 w = raw(cfg, 16u + b);
         return make_float4(u01(w.x), u01(w.y), u01(w.z), u01(w.w));
     }
 };
-__device__ __forceinline__ Rng make_rng(const DevCfg& cfg, long long gid, uint32_t ctr, uint32_t tag) {
+__device__ __forceinline__ Rng make_rng(long long gid, uint32_t ctr, uint32_t tag) {
     Rng r;
-    r.k0 = cfg.seed_lo; r.k1 = cfg.seed_hi;
     r.c0 = (uint32_t)gid; r.c1 = ctr;
     r.c3 = tag ^ ((uint32_t)((unsigned long long)gid >> 32) << 8);
     return r;
 }
 
-// Standard draws of one event: either generated (Philox) or read from the injected slot-major
-// buffers [slot][n] (parity mode).  NZ/NU are compile-time slot counts.
-template <int NZ, int NU>
-struct Draws {
-    float z[NZ];
-    float u[NU];
-    __device__ __forceinline__ void generate(const Rng& rng) {
-#pragma unroll
-        for (int b = 0; 4 * b < NZ; ++b) {
-            float4 v = rng.normals(b);
-            z[4 * b] = v.x;
-            if (4 * b + 1 < NZ) z[4 * b + 1] = v.y;
-            if (4 * b + 2 < NZ) z[4 * b + 2] = v.z;
-            if (4 * b + 3 < NZ) z[4 * b + 3] = v.w;
+// Standard draws of one event, fetched four at a time where they are consumed: generated
+// (Philox) or read from the injected slot-major buffers [slot][n] (parity mode).
+struct DrawSrc {
+    Rng rng;
+    const float* iz;      // injected normals  [nz][n] or null
+    const float* iu;      // injected uniforms [nu][n]
+    int n, i, nu;
+    __device__ __forceinline__ float4 z(const DevCfg& cfg, int b) const {
+        if (iz) {
+            const float* p = iz + (size_t)(4 * b) * n + i;
+            return make_float4(p[0], p[n], p[2 * (size_t)n], p[3 * (size_t)n]);
         }
-#pragma unroll
-        for (int b = 0; 4 * b < NU; ++b) {
-            float4 v = rng.uniforms(b);
-            u[4 * b] = v.x;
-            if (4 * b + 1 < NU) u[4 * b + 1] = v.y;
-            if (4 * b + 2 < NU) u[4 * b + 2] = v.z;
-            if (4 * b + 3 < NU) u[4 * b + 3] = v.w;
-        }
+        return rng.normals(cfg, b);
     }
-    __device__ __forceinline__ void load(const float* zbuf, const float* ubuf, int n, int i) {
-#pragma unroll
-        for (int s = 0; s < NZ; ++s) z[s] = zbuf[(size_t)s * n + i];
-#pragma unroll
-        for (int s = 0; s < NU; ++s) u[s] = ubuf[(size_t)s * n + i];
+    __device__ __forceinline__ float4 u(const DevCfg& cfg, int b) const {
+        if (iu) {
+            const float* p = iu + (size_t)(4 * b) * n + i;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (4 * b < nu) v.x = p[0];
+            if (4 * b + 1 < nu) v.y = p[n];
+            if (4 * b + 2 < nu) v.z = p[2 * (size_t)n];
+            if (4 * b + 3 < nu) v.w = p[3 * (size_t)n];
+            return v;
+        }
+        return rng.uniforms(cfg, b);
     }
 };
+__device__ __forceinline__ DrawSrc make_draws(const DevCfg& cfg, long long gid, uint32_t ctr, uint32_t tag,
+                                              const float* iz, const float* iu, int n, int i, int nu) {
+    DrawSrc d;
+    d.rng = make_rng(gid, ctr, tag);
+    d.iz = cfg.injected ? iz : nullptr;
+    d.iu = cfg.injected ? iu : nullptr;
+    d.n = n; d.i = i; d.nu = nu;
+    return d;
+}
 
-// ---------------------------------------------------------------------------------- state
-struct alignas(16) Env {
-    float pos[3], ep_ret, quat[4], vel[3], ow[3], lpf[3], bias[3];
-    float x[4], ou[4], ring[8], ap1[4], ap2[4], obs_prev[13];
-    int ep_len; uint32_t rng_ctr, misc;
-    float dt, mass, J[3], ftf1, B[4], K[4];
+// ---------------------------------------------------------------------------------- state access
+// Word w of this thread's env: p[w * CF_TILE].  p points into the shared-memory copy of the tile
+// (step kernel, words 0..CF_DYN_WORDS-1) or into the tile in HBM (all 76 words).
+struct EnvRef {
+    float* p;
+    __device__ __forceinline__ float f(int w) const { return p[w * CF_TILE]; }
+    __device__ __forceinline__ void f(int w, float v) const { p[w * CF_TILE] = v; }
+    __device__ __forceinline__ uint32_t u(int w) const { return __float_as_uint(p[w * CF_TILE]); }
+    __device__ __forceinline__ void u(int w, uint32_t v) const { p[w * CF_TILE] = __uint_as_float(v); }
+    __device__ __forceinline__ void get3(int w, float v[3]) const { v[0] = f(w); v[1] = f(w + 1); v[2] = f(w + 2); }
+    __device__ __forceinline__ void get4(int w, float v[4]) const { v[0] = f(w); v[1] = f(w + 1); v[2] = f(w + 2); v[3] = f(w + 3); }
+    __device__ __forceinline__ void set3(int w, const float v[3]) const { f(w, v[0]); f(w + 1, v[1]); f(w + 2, v[2]); }
+    __device__ __forceinline__ void set4(int w, const float v[4]) const { f(w, v[0]); f(w + 1, v[1]); f(w + 2, v[2]); f(w + 3, v[3]); }
 };
-static_assert(sizeof(Env) == CF_STATE_WORDS * 4, "Env must mirror the CF_S_* record");
+// global-memory address of env i's word 0 in the tiled state array
+__device__ __forceinline__ float* env_global(float* S, int i) {
+    return S + (size_t)(i / CF_TILE) * (CF_STATE_WORDS * CF_TILE) + (i % CF_TILE);
+}
+
+// domain-randomised parameters (words CF_S_DT..): read-only in the step, rewritten by reset
+struct DrParams {
+    float dt, mass, J[3], ftf1, B[4], K[4];
+    __device__ __forceinline__ void load(const EnvRef g) {
+        dt = g.f(CF_S_DT); mass = g.f(CF_S_MASS); g.get3(CF_S_INERTIA, J); ftf1 = g.f(CF_S_FTF1);
+        g.get4(CF_S_MOTOR_B, B); g.get4(CF_S_MOTOR_K, K);
+    }
+    __device__ __forceinline__ void store(const EnvRef g) const {
+        g.f(CF_S_DT, dt); g.f(CF_S_MASS, mass); g.set3(CF_S_INERTIA, J); g.f(CF_S_FTF1, ftf1);
+        g.set4(CF_S_MOTOR_B, B); g.set4(CF_S_MOTOR_K, K);
+    }
+};
 
 // misc word: level_idx | ring_idx<<8 | iteration<<12 | fresh<<31   (cf_abi.h CF_S_MISC)
 __device__ __forceinline__ int misc_level(uint32_t m) { return (int)(m & 0xffu); }
@@ -112,17 +150,12 @@ __device__ __forceinline__ uint32_t misc_pack(int level, int ring, int iter, boo
     return (uint32_t)level | ((uint32_t)ring << 8) | ((uint32_t)(iter & 1) << 12) | (fresh ? 0x80000000u : 0u);
 }
 
-// HBM layout: float4 S[kGroups][n_envs]; group g of env i holds record words 4g..4g+3.
-// Every load/store below is one 128-bit access per thread, 512 contiguous bytes per warp.
-__device__ __forceinline__ void load_env(Env& e, const float4* __restrict__ S, int n, int i) {
-    float4* w = reinterpret_cast<float4*>(&e);
+// 64-bit stores of an 8-byte aligned row (obs rows are 136 B or 168 B)
+template <int DIM>
+__device__ __forceinline__ void store_row(float* __restrict__ dst, const float* v) {
+    float2* p = reinterpret_cast<float2*>(dst);
 #pragma unroll
-    for (int g = 0; g < kGroups; ++g) w[g] = S[(size_t)g * n + i];
-}
-__device__ __forceinline__ void store_env(const Env& e, float4* __restrict__ S, int n, int i) {
-    const float4* w = reinterpret_cast<const float4*>(&e);
-#pragma unroll
-    for (int g = 0; g < kGroups; ++g) S[(size_t)g * n + i] = w[g];
+    for (int k = 0; k < DIM / 2; ++k) p[k] = make_float2(v[2 * k], v[2 * k + 1]);
 }
 
 // ---------------------------------------------------------------------------------- kinematics
@@ -183,13 +216,6 @@ __device__ __forceinline__ void quat2euler_hj(const float q[4], float out[3]) {
     out[1] = asinf(t2);
     out[2] = atan2f(2.0f * (w * z + x * y), 1.0f - 2.0f * (y * y + z * z));
 }
-// true-state attitude and body rates as CrazyFlieAgent.update_information exposes them (agents.py:434-453)
-__device__ __forceinline__ void body_rates(const Env& e, float rpy[3], float wb[3]) {
-    float R[9];
-    quat_to_rpy_bullet(e.quat, rpy);
-    quat_to_R(e.quat, R);
-    matTvec(R, e.ow, wb);
-}
 
 // ---------------------------------------------------------------------------------- HJ lookup
 // Grid.get_index (odp/Grid/GridProcessing.py:53-72): np.searchsorted(side='left') on the float64
@@ -204,6 +230,18 @@ __device__ __forceinline__ int hj_index_dim(double s, int d) {
     while (i > 0 && !(g[i - 1] < s)) --i;
     if (i > 0 && (i == 15 || fabs(s - g[i - 1]) < fabs(s - g[i]))) i -= 1;
     return i;
+}
+// The same index for a float32 state, without float64: the rule above is monotone in s, so for
+// each cell boundary j the host finds (by bisection over float32 values, with the float64 rule)
+// the smallest float32 whose index is >= j+1; index = #{j : s >= thr[d][j]}.  thr is [6][16]
+// (14 thresholds, NaN, NaN) in shared or global memory; lo/inv_dx give a guess within +-1.
+__device__ __forceinline__ int hj_index_f32(float s, int d, const float* __restrict__ thr, const DevCfg& cfg) {
+    const float* t = thr + 16 * d;
+    float g = clampf((s - cfg.hj_lo[d]) * cfg.hj_inv_dx[d], 0.0f, 14.0f);
+    int i = (int)(g + 0.5f);
+    if (s >= t[i]) i += 1;                  /* t[14] = t[15] = NaN: never true */
+    else if (i > 0 && s < t[i - 1]) i -= 1;
+    return (s != s) ? CF_HJ_PTS - 1 : i;
 }
 __device__ __forceinline__ float sgnf(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
 // spa_deriv for one non-periodic dim (distur_gener.py:40-99) and the `> 0` test of opt_dstb_non_hcl
@@ -227,8 +265,8 @@ __device__ __forceinline__ bool hj_deriv_positive(const float* __restrict__ V, l
     double left = (double)a / dx, right = (double)b / dx;
     return (left + right) / 2.0 > 0.0;
 }
-__device__ __forceinline__ long hj_cell(const int idx[6]) {
-    return ((((long)idx[0] * 15 + idx[1]) * 15 + idx[2]) * 15 + idx[3]) * 15 * 15 + (long)idx[4] * 15 + idx[5];
+__device__ __forceinline__ int hj_cell(const int idx[6]) {
+    return ((((idx[0] * 15 + idx[1]) * 15 + idx[2]) * 15 + idx[3]) * 15 + idx[4]) * 15 + idx[5];
 }
 // bit0: dV/dx3 > 0, bit1: dV/dx4 > 0
 __device__ __forceinline__ int hj_signbits_value(const float* __restrict__ V, const int idx[6]) {
@@ -238,56 +276,55 @@ __device__ __forceinline__ int hj_signbits_value(const float* __restrict__ V, co
     return b0 | b1;
 }
 __device__ __forceinline__ int hj_signbits_packed(const uint8_t* __restrict__ P, const int idx[6]) {
-    long c = hj_cell(idx);
-    return (__ldg(P + (c >> 2)) >> (2 * (int)(c & 3))) & 3;
+    int c = hj_cell(idx);
+    return (__ldg(P + (c >> 2)) >> (2 * (c & 3))) & 3;
 }
-// distur_gener (distur_gener.py:19-183) reduced to the two torque components the physics uses
 template <int HJ_MODE>
-__device__ __forceinline__ void hj_disturbance(const Env& e, const DevTables& tab, int level_idx, float d[2],
-                                               int* idx_out) {
+__device__ __forceinline__ int hj_signbits(const DevTables& tab, int level_idx, const int idx[6]) {
+    if (HJ_MODE == CF_HJ_SIGN_TABLE) return hj_signbits_packed(tab.signs + (size_t)level_idx * CF_SIGN_STRIDE, idx);
+    return hj_signbits_value(tab.value[level_idx], idx);
+}
+// distur_gener (distur_gener.py:19-183) reduced to the two torque components the physics uses:
+// returns the sign bits of the level's table at the nearest grid cell of (rpy, body rates)
+template <int HJ_MODE>
+__device__ __forceinline__ int hj_disturbance_bits(const float q[4], const float ow[3], const DevCfg& cfg,
+                                                   const DevTables& tab, const float* thr, int level_idx) {
     float rpy[3], R[9], wb[3];
-    quat2euler_hj(e.quat, rpy);
-    quat_to_R(e.quat, R);
-    matTvec(R, e.ow, wb);
+    quat2euler_hj(q, rpy);
+    quat_to_R(q, R);
+    matTvec(R, ow, wb);
     int idx[6];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { idx[k] = hj_index_dim((double)rpy[k], k); idx[3 + k] = hj_index_dim((double)wb[k], 3 + k); }
-    int bits;
-    if (HJ_MODE == CF_HJ_SIGN_TABLE) bits = hj_signbits_packed(tab.signs[level_idx], idx);
-    else bits = hj_signbits_value(tab.value[level_idx], idx);
-    float dmax = ((float)level_idx / 10.0f) * 5.3e-3f;          // distur_gener.py:152,160
-    d[0] = (bits & 1) ? -dmax : dmax;
-    d[1] = (bits & 2) ? -dmax : dmax;
-    if (idx_out) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) idx_out[k] = idx[k];
-    }
+    for (int k = 0; k < 3; ++k) { idx[k] = hj_index_f32(rpy[k], k, thr, cfg); idx[3 + k] = hj_index_f32(wb[k], 3 + k, thr, cfg); }
+    return hj_signbits<HJ_MODE>(tab, level_idx, idx);
 }
 
 // ---------------------------------------------------------------------------------- sensors
 // SensorNoise.add_noise_to_omega (envs/sensors.py:121-134) at dt = 1/SIM_FREQ, followed by
 // LowPassFilter.apply (envs/utils.py:102-105, ratio T_s/T = 0.5; base.py:107).
-// z: bias-walk 3, random-walk 3, turn-on 3 standard normals.
-__device__ __forceinline__ void gyro_update(Env& e, const DevCfg& cfg, const float wb[3],
+// zb, zr, zt: bias-walk, random-walk, turn-on standard normals.
+__device__ __forceinline__ void gyro_update(float bias[3], float lpf[3], const DevCfg& cfg, const float wb[3],
                                             const float zb[3], const float zr[3], const float zt[3]) {
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        e.bias[i] = cfg.gyro_pi * e.bias[i] + cfg.gyro_sb * zb[i];
-        float om = ((wb[i] + e.bias[i]) + cfg.gyro_rw * zr[i]) + cfg.gyro_ton * zt[i];
-        e.lpf[i] = 0.5f * e.lpf[i] + 0.5f * om;
+        bias[i] = cfg.gyro_pi * bias[i] + cfg.gyro_sb * zb[i];
+        float om = ((wb[i] + bias[i]) + cfg.gyro_rw * zr[i]) + cfg.gyro_ton * zt[i];
+        lpf[i] = 0.5f * lpf[i] + 0.5f * om;
     }
 }
 // The 100 Hz branch of compute_observation (hover_free.py:168-200) with SensorNoise.add_noise
-// (sensors.py:75-119): z = pos3, vel3, gyro9, rot3; u = pos3, rot3.  Writes obs13.
-__device__ __forceinline__ void observe_full(Env& e, const DevCfg& cfg, const float rpy[3], const float wb[3],
-                                             const float* z, const float* u, float obs[13]) {
+// (sensors.py:75-119).  Normal blocks zb0.. cover 18 slots starting at slot offset `off` inside
+// block zb0: pos3, vel3, gyro9 (bias, random walk, turn-on), rot3; uniforms: pos3, rot3.
+__device__ __forceinline__ void observe_full(const float pos[3], const float vel[3], const float rpy[3], const float wb[3],
+                                             float bias[3], float lpf[3], const DevCfg& cfg, const float z[18],
+                                             const float u[6], float obs[13]) {
     const float kPosStd = 0.002f, kPosUnif = 0.001f, kVelStd = 0.01f;     // sensors.py:18-25
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        obs[i] = e.pos[i] + (kPosStd * z[i] + (-kPosUnif + (2.0f * kPosUnif) * u[i]));
-        obs[7 + i] = e.vel[i] + kVelStd * z[3 + i];                        // vel_unif_range = 0
+        obs[i] = pos[i] + (kPosStd * z[i] + (-kPosUnif + (2.0f * kPosUnif) * u[i]));
+        obs[7 + i] = vel[i] + kVelStd * z[3 + i];                          // vel_unif_range = 0
     }
-    gyro_update(e, cfg, wb, z + 6, z + 9, z + 12);
+    gyro_update(bias, lpf, cfg, wb, z + 6, z + 9, z + 12);
     const float lo[3] = {-kPi, -0.5f * kPi, -kPi}, hi[3] = {kPi, 0.5f * kPi, kPi};
     float rot[3];
 #pragma unroll
@@ -297,59 +334,61 @@ __device__ __forceinline__ void observe_full(Env& e, const DevCfg& cfg, const fl
     }
     rpy_to_quat(rot, obs + 3);
 #pragma unroll
-    for (int i = 0; i < 3; ++i) obs[10 + i] = e.lpf[i];
+    for (int i = 0; i < 3; ++i) obs[10 + i] = lpf[i];
 }
 
 // ---------------------------------------------------------------------------------- physics substep
+// Rigid-body + motor state held in registers across the two substeps of a control step.
+struct Body {
+    float pos[3], quat[4], vel[3], ow[3], x[4], ou[4];
+};
 // PybulletPhysicsWithAdversary.step_forward (envs/physics.py:213-250) with
 // CrazyFlieAgent.apply_action (agents.py:259-298), PWM.act (control.py:94-100), OUNoise.noise
 // (envs/utils.py:128-133) and Bullet's stepSimulation as restated by the oracle (B1-B9:
 // semi-implicit Euler, exponential-map quaternion update, gyroscopic term, 0.04 damping).
-__device__ __forceinline__ void physics_substep(Env& e, const DevCfg& cfg, const float a[4], const float d[2],
+// `delayed` is the action leaving the latency ring in this substep (agents.py:268-276);
+// invJ / invm are reciprocals of the (domain-randomised) inertia and mass.
+__device__ __forceinline__ void physics_substep(Body& b, const DrParams& p, const float invJ[3], float invm,
+                                                const DevCfg& cfg, const float delayed[4], float d0, float d1,
                                                 const float zou[4]) {
     const float kFtf0 = 1.56e-5f, kArm = 0.028f, kPropZ = 0.0108f, kG = 9.81f;
     const float kDrag[3] = {9.1785e-7f, 9.1785e-7f, 10.311e-7f};
-    // latency ring (agents.py:268-276): read the delayed action, then overwrite the slot
-    int ridx = misc_ring(e.misc);
     float f[4], t[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float delayed = ridx ? e.ring[4 + i] : e.ring[i];
-        if (ridx) e.ring[4 + i] = a[i]; else e.ring[i] = a[i];
-        float c = fminf(1.0f, fmaxf(-1.0f, delayed));
-        float pwm = 30000.0f + c * 30000.0f;
-        e.ou[i] = e.ou[i] + (0.15f * (0.0f - e.ou[i]) + cfg.ou_sigma * zou[i]);
-        float rot = sqrtf(pwm / 60000.0f);
-        e.x[i] = (1.0f - e.B[i]) * e.x[i] + e.B[i] * rot;
-        float noisy = (1.0f + e.ou[i]) * (e.x[i] * e.x[i]);
-        float nn = fminf(1.0f, fmaxf(0.0f, noisy));
-        f[i] = e.K[i] * nn;
-        t[i] = e.ftf1 * f[i] + kFtf0;
-    }
-    e.misc ^= (1u << 8);                                    // action_idx = (action_idx + 1) % 2
-    float zt = ((-t[0] + t[1]) - t[2]) + t[3];
-    float R[9], wb[3], vb[3];
-    quat_to_R(e.quat, R);
-    matTvec(R, e.ow, wb);
-    matTvec(R, e.vel, vb);
-    // drag (physics.py:232-241): R @ (k * v_world) handed to Bullet as a LINK_FRAME force
     float rpm_sum = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) rpm_sum += 2.0f * kPi * ((e.x[i] * e.x[i]) * 25000.0f) / 60.0f;
+    for (int i = 0; i < 4; ++i) {
+        float c = clampf(delayed[i], -1.0f, 1.0f);
+        float pwm = 30000.0f + c * 30000.0f;
+        b.ou[i] = b.ou[i] + (0.15f * (0.0f - b.ou[i]) + cfg.ou_sigma * zou[i]);
+        float rot = fsqrt(pwm * (1.0f / 60000.0f));
+        b.x[i] = (1.0f - p.B[i]) * b.x[i] + p.B[i] * rot;
+        float xx = b.x[i] * b.x[i];
+        float nn = clampf((1.0f + b.ou[i]) * xx, 0.0f, 1.0f);
+        f[i] = p.K[i] * nn;
+        t[i] = p.ftf1 * f[i] + kFtf0;
+        rpm_sum += xx;
+    }
+    rpm_sum *= 2.0f * kPi * 25000.0f / 60.0f;                 // sum_i 2 pi (25000 x_i^2) / 60, physics.py:236
+    float zt = ((-t[0] + t[1]) - t[2]) + t[3];
+    float R[9], wb[3], vb[3];
+    quat_to_R(b.quat, R);
+    matTvec(R, b.ow, wb);
+    matTvec(R, b.vel, vb);
+    // drag (physics.py:232-241): R @ (k * v_world) handed to Bullet as a LINK_FRAME force
     float kv[3], drag_link[3];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) kv[i] = (-1.0f * kDrag[i] * rpm_sum) * e.vel[i];
+    for (int i = 0; i < 3; ++i) kv[i] = (-1.0f * kDrag[i] * rpm_sum) * b.vel[i];
     matvec(R, kv, drag_link);
     float fe[4] = {f[0], f[1], f[2], f[3]};
     if (cfg.ground_effect) {                               // physics.py:27-58; reference leaves it off
         const float kPx[4] = {0.028f, -0.028f, -0.028f, 0.028f}, kPy[4] = {-0.028f, -0.028f, 0.028f, 0.028f};
         const float kGnd = 11.36859f, kPropR = 2.31348e-2f;
         float rpy[3];
-        quat_to_rpy_bullet(e.quat, rpy);
+        quat_to_rpy_bullet(b.quat, rpy);
         if (fabsf(rpy[0]) < 0.5f * kPi && fabsf(rpy[1]) < 0.5f * kPi) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                float pz = e.pos[2] + R[6] * kPx[i] + R[7] * kPy[i] + R[8] * kPropZ;
+                float pz = b.pos[2] + R[6] * kPx[i] + R[7] * kPy[i] + R[8] * kPropZ;
                 pz = fmaxf(pz, cfg.gnd_hclip);
                 float q = kPropR / (4.0f * pz);
                 fe[i] += f[i] * kGnd * (q * q);
@@ -358,50 +397,53 @@ __device__ __forceinline__ void physics_substep(Env& e, const DevCfg& cfg, const
     }
     // body-frame wrench: thrust at the prop positions (agents.py:311-321, urdf:59,85,111,136),
     // yaw torque (:330-337), adversary roll/pitch torques (:517-533)
-    float tau[3] = {kArm * (-fe[0] - fe[1] + fe[2] + fe[3]) + d[0],
-                    kArm * (-fe[0] + fe[1] + fe[2] - fe[3]) + d[1], zt};
+    float tau[3] = {kArm * (-fe[0] - fe[1] + fe[2] + fe[3]) + d0,
+                    kArm * (-fe[0] + fe[1] + fe[2] - fe[3]) + d1, zt};
     float fb[3] = {drag_link[0], drag_link[1], drag_link[2] + (fe[0] + fe[1] + fe[2] + fe[3])};
-    float gz = -kG * e.mass;
+    float gz = -kG * p.mass;
     float gb[3] = {R[6] * gz, R[7] * gz, R[8] * gz};        // R^T (0,0,-g m)
-    float Jw[3] = {e.J[0] * wb[0], e.J[1] * wb[1], e.J[2] * wb[2]};
+    float Jw[3] = {p.J[0] * wb[0], p.J[1] * wb[1], p.J[2] * wb[2]};
     if (cfg.gyroscopic) {
         tau[0] -= wb[1] * Jw[2] - wb[2] * Jw[1];
         tau[1] -= wb[2] * Jw[0] - wb[0] * Jw[2];
         tau[2] -= wb[0] * Jw[1] - wb[1] * Jw[0];
     }
-    float wn = sqrtf(wb[0] * wb[0] + wb[1] * wb[1] + wb[2] * wb[2]);
-    float vn = sqrtf(vb[0] * vb[0] + vb[1] * vb[1] + vb[2] * vb[2]);
+    float wn = fsqrt(wb[0] * wb[0] + wb[1] * wb[1] + wb[2] * wb[2]);
+    float vn = fsqrt(vb[0] * vb[0] + vb[1] * vb[1] + vb[2] * vb[2]);
     float ka = cfg.ang_damp, kl = cfg.lin_damp;
     float alpha_b[3], acc_b[3], alpha_w[3], acc_w[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        alpha_b[i] = (tau[i] - Jw[i] * (ka + ka * wn)) / e.J[i];
-        acc_b[i] = ((fb[i] + gb[i]) - e.mass * vb[i] * (kl + kl * vn)) / e.mass;
+        alpha_b[i] = (tau[i] - Jw[i] * (ka + ka * wn)) * invJ[i];
+        acc_b[i] = ((fb[i] + gb[i]) - p.mass * vb[i] * (kl + kl * vn)) * invm;
     }
     matvec(R, alpha_b, alpha_w);
     matvec(R, acc_b, acc_w);
-    float dt = e.dt;
+    float dt = p.dt;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        e.ow[i] += dt * alpha_w[i];
-        e.vel[i] += dt * acc_w[i];
-        e.pos[i] += dt * e.vel[i];
+        b.ow[i] += dt * alpha_w[i];
+        b.vel[i] += dt * acc_w[i];
+        b.pos[i] += dt * b.vel[i];
     }
-    // exponential-map quaternion update (btMultiBody::stepPositionsMultiDof)
-    float w0 = e.ow[0], w1 = e.ow[1], w2 = e.ow[2];
-    float ang = sqrtf(w0 * w0 + w1 * w1 + w2 * w2), s, cw;
-    if (ang * dt > 0.25f * kPi) ang = 0.25f * kPi / dt;
-    if (ang < 0.001f) { s = 0.5f * dt - (dt * dt * dt) * 0.020833333333f * ang * ang; cw = cosf(ang * dt * 0.5f); }
-    else { float sn; sincosf(0.5f * ang * dt, &sn, &cw); s = sn / ang; }
+    // exponential-map quaternion update (btMultiBody::stepPositionsMultiDof): dq = (w sin(h)/|w|, cos(h)),
+    // h = |w| dt / 2 clamped to pi/8.  sin(h)/h and cos(h) as even polynomials in h (|h| <= pi/8: truncation
+    // < 2e-9), which is also Bullet's own small-angle branch; no range reduction, no division.
+    float w0 = b.ow[0], w1 = b.ow[1], w2 = b.ow[2];
+    float h = fminf(0.5f * dt * fsqrt(w0 * w0 + w1 * w1 + w2 * w2), 0.125f * kPi);   // Bullet clamps the angle only
+    float h2 = h * h;
+    float sinc = 1.0f + h2 * (-1.0f / 6.0f + h2 * (1.0f / 120.0f + h2 * (-1.0f / 5040.0f + h2 * (1.0f / 362880.0f))));
+    float cw = 1.0f + h2 * (-0.5f + h2 * (1.0f / 24.0f + h2 * (-1.0f / 720.0f + h2 * (1.0f / 40320.0f))));
+    float s = (0.5f * dt) * sinc;                           // sin(h) / (2h/dt): Bullet divides by the clamped rate
     float dq[4] = {w0 * s, w1 * s, w2 * s, cw}, q[4];
-    const float* b = e.quat;
-    q[0] = dq[3] * b[0] + dq[0] * b[3] + dq[1] * b[2] - dq[2] * b[1];
-    q[1] = dq[3] * b[1] - dq[0] * b[2] + dq[1] * b[3] + dq[2] * b[0];
-    q[2] = dq[3] * b[2] + dq[0] * b[1] - dq[1] * b[0] + dq[2] * b[3];
-    q[3] = dq[3] * b[3] - dq[0] * b[0] - dq[1] * b[1] - dq[2] * b[2];
+    const float* bq = b.quat;
+    q[0] = dq[3] * bq[0] + dq[0] * bq[3] + dq[1] * bq[2] - dq[2] * bq[1];
+    q[1] = dq[3] * bq[1] - dq[0] * bq[2] + dq[1] * bq[3] + dq[2] * bq[0];
+    q[2] = dq[3] * bq[2] + dq[0] * bq[1] - dq[1] * bq[0] + dq[2] * bq[3];
+    q[3] = dq[3] * bq[3] - dq[0] * bq[0] - dq[1] * bq[1] - dq[2] * bq[2];
     float inv = rsqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) e.quat[i] = q[i] * inv;
+    for (int i = 0; i < 4; ++i) b.quat[i] = q[i] * inv;
 }
 
 // ---------------------------------------------------------------------------------- reset
@@ -411,41 +453,62 @@ __device__ __forceinline__ float dr_draw(float def, float f, float u) { float b 
 // Constructor state of an env (DroneBaseEnv.__init__ + CrazyFlieAgent.__init__): zero state at
 // (0,0,1), nominal parameters; `fresh` marks that the constructor-time compute_observation()
 // (base.py:141), which advances gyro_bias once, has not been accounted for yet.
-__device__ __forceinline__ void init_env(Env& e, const DevCfg& cfg) {
-    float* w = reinterpret_cast<float*>(&e);
+__device__ __forceinline__ void init_env(const EnvRef e, const DevCfg& cfg) {
 #pragma unroll
-    for (int k = 0; k < CF_STATE_WORDS; ++k) w[k] = 0.0f;
-    e.pos[2] = 1.0f; e.quat[3] = 1.0f;
-    e.dt = cfg.sim_dt; e.mass = 0.030f;
-    e.J[0] = 1.33e-5f; e.J[1] = 1.33e-5f; e.J[2] = 2.64e-5f;
-    e.ftf1 = 5.96e-3f;
+    for (int k = 0; k < CF_STATE_WORDS; ++k) e.f(k, 0.0f);
+    e.f(CF_S_POS + 2, 1.0f); e.f(CF_S_QUAT + 3, 1.0f);
+    e.f(CF_S_DT, cfg.sim_dt); e.f(CF_S_MASS, 0.030f);
+    e.f(CF_S_INERTIA, 1.33e-5f); e.f(CF_S_INERTIA + 1, 1.33e-5f); e.f(CF_S_INERTIA + 2, 2.64e-5f);
+    e.f(CF_S_FTF1, 5.96e-3f);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { e.B[i] = cfg.nomB; e.K[i] = cfg.nomK; }
-    e.ep_len = 0; e.rng_ctr = 0u;
-    e.misc = misc_pack(cfg.fixed_level_idx, 0, 0, true);
+    for (int i = 0; i < 4; ++i) { e.f(CF_S_MOTOR_B + i, cfg.nomB); e.f(CF_S_MOTOR_K + i, cfg.nomK); }
+    e.u(CF_S_EP_LEN, 0u); e.u(CF_S_RNG_CTR, 0u);
+    e.u(CF_S_MISC, misc_pack(cfg.fixed_level_idx, 0, 0, true));
+}
+
+// constructor-time compute_observation() (base.py:141): gyro_bias <- sigma_b * N(0,1), event tag 3
+__device__ __forceinline__ void consume_fresh(const EnvRef e, const DevCfg& cfg, long long gid, bool noise) {
+    uint32_t m = e.u(CF_S_MISC);
+    if (!misc_fresh(m)) return;
+    if (noise && !cfg.injected) {
+        float4 z = make_rng(gid, 0u, 3u).normals(cfg, 0);
+        e.f(CF_S_GYRO_BIAS, cfg.gyro_sb * z.x); e.f(CF_S_GYRO_BIAS + 1, cfg.gyro_sb * z.y); e.f(CF_S_GYRO_BIAS + 2, cfg.gyro_sb * z.z);
+    }
+    e.u(CF_S_MISC, m & 0x7fffffffu);
+}
+
+// All standard draws of a reset event, slot order of the oracle: z[48], u[44] (42 used).
+__device__ __forceinline__ void reset_draws(const DrawSrc& dw, const DevCfg& cfg, float* z, float* u) {
+#pragma unroll
+    for (int b = 0; b < CF_RESET_NORMALS / 4; ++b) { float4 v = dw.z(cfg, b); z[4 * b] = v.x; z[4 * b + 1] = v.y; z[4 * b + 2] = v.z; z[4 * b + 3] = v.w; }
+#pragma unroll
+    for (int b = 0; b < (CF_RESET_UNIFORMS + 3) / 4; ++b) { float4 v = dw.u(cfg, b); u[4 * b] = v.x; u[4 * b + 1] = v.y; u[4 * b + 2] = v.z; u[4 * b + 3] = v.w; }
 }
 
 // reset(): envs/base.py:420-464, task_specific_reset hover_free.py:237-289 / hover.py:1463-1513,
 // apply_domain_randomization base.py:241-298 (+ agents.py:208-224), RandomHJ level draw
 // hover_free.py:536.  Draw slots: z[0:4] motor x, z[4:12] latency ring, z[12:30] and z[30:48]
 // the two compute_observation calls; u[0:14] initial state, u[14:29] DR, u[29:35], u[35:41]
-// observation uniforms, u[41] Boltzmann.  obs: obs_dim floats.
+// observation uniforms, u[41] Boltzmann.  `e` holds the dynamic words (shared or global), `g` the
+// env in global memory (the domain-randomised words are written there); nz / un: the event's
+// standard draws (shared-memory scratch filled by the warp, or thread-local); row: obs_dim floats.
 template <bool NOISE>
-__device__ __forceinline__ void reset_env(Env& e, const DevCfg& cfg, const Draws<CF_RESET_NORMALS, CF_RESET_UNIFORMS>& dw,
-                                          float* obs) {
-    const float* nz = dw.z;
-    const float* un = dw.u;
+__device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const DevCfg& cfg, const float* nz, const float* un,
+                                          float* row) {
+    constexpr int OD = NOISE ? 34 : 42;
     // stale body rate of the previous state, read before anything moves (base.py:444 before :448)
-    float stale_rpy[3], stale_wb[3];
-    body_rates(e, stale_rpy, stale_wb);
-    int level = misc_level(e.misc);
-    e.ep_len = 0; e.ep_ret = 0.0f;
-    // drone.reset(), agents.py:377-386
-#pragma unroll
-    for (int i = 0; i < 4; ++i) e.x[i] = 0.0f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) e.ring[i] = 0.0f;
+    float stale_wb[3];
+    {
+        float q[4], ow[3], R[9];
+        e.get4(CF_S_QUAT, q); e.get3(CF_S_OMEGA_W, ow);
+        quat_to_R(q, R);
+        matTvec(R, ow, stale_wb);
+    }
+    int level = misc_level(e.u(CF_S_MISC));
+    e.u(CF_S_EP_LEN, 0u); e.f(CF_S_EP_RET, 0.0f);
+    // drone.reset(), agents.py:377-386, then task_specific_reset
     float pos[3] = {0.f, 0.f, 1.f}, rpy[3] = {0.f, 0.f, 0.f}, vel[3] = {0.f, 0.f, 0.f}, rate[3] = {0.f, 0.f, 0.f};
+    float quat[4] = {0.f, 0.f, 0.f, 1.f}, x[4] = {0.f, 0.f, 0.f, 0.f}, la[4] = {0.f, 0.f, 0.f, 0.f};
     if (cfg.reset_dist) {
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
@@ -457,177 +520,245 @@ __device__ __forceinline__ void reset_env(Env& e, const DevCfg& cfg, const Draws
         rpy[2] = unif(-cfg.init_yaw, cfg.init_yaw, un[6]);
         rate[2] = unif(-cfg.init_yaw_rate, cfg.init_yaw_rate, un[13]);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) e.x[i] = cfg.hover_x + 0.02f * nz[i];
+        for (int i = 0; i < 4; ++i) x[i] = cfg.hover_x + 0.02f * nz[i];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) e.ring[i] = fminf(1.0f, fmaxf(-1.0f, cfg.hover_a + 0.02f * nz[4 + i]));
-        rpy_to_quat(rpy, e.quat);
+        for (int i = 0; i < 8; ++i) {
+            float r = clampf(cfg.hover_a + 0.02f * nz[4 + i], -1.0f, 1.0f);
+            e.f(CF_S_RING + i, r);
+            if (i >= 4) la[i - 4] = r;                      // view of action_buffer[-1,:], agents.py:386
+        }
+        rpy_to_quat(rpy, quat);
     } else {
-        e.quat[0] = e.quat[1] = e.quat[2] = 0.0f; e.quat[3] = 1.0f;
-    }
 #pragma unroll
-    for (int i = 0; i < 3; ++i) { e.pos[i] = pos[i]; e.vel[i] = vel[i]; }
-    {   // resetBaseVelocity(angularVelocity = R.T @ rpy_dot), hover_free.py:283-289
-        float R[9];
-        quat_to_R(e.quat, R);
-        matTvec(R, rate, e.ow);
+        for (int i = 0; i < 8; ++i) e.f(CF_S_RING + i, 0.0f);
     }
+    e.set3(CF_S_POS, pos); e.set4(CF_S_QUAT, quat); e.set3(CF_S_VEL, vel); e.set4(CF_S_MOTOR_X, x);
+    float R[9], ow[3], wb[3];
+    quat_to_R(quat, R);
+    matTvec(R, rate, ow);                                   // resetBaseVelocity(angularVelocity = R.T @ rpy_dot), hover_free.py:283-289
+    e.set3(CF_S_OMEGA_W, ow);
+    matTvec(R, ow, wb);                                     // update_information: R.T again (agents.py:452-453)
     if (cfg.dr_on) {
+        // un[14..28]: dt, mass, Jxx, Jyy, Jzz, (ftf0: cancels in the yaw torque), ftf1, motor tc[4], t2w[4]
         float f = cfg.dr;
-        e.dt = dr_draw(cfg.sim_dt, f, un[14]);
-        e.mass = dr_draw(0.030f, f, un[15]);
-        e.J[0] = dr_draw(1.33e-5f, f, un[16]);
-        e.J[1] = dr_draw(1.33e-5f, f, un[17]);
-        e.J[2] = dr_draw(2.64e-5f, f, un[18]);
-        e.ftf1 = dr_draw(5.96e-3f, f, un[20]);          // un[19]: force_torque_factor_0, cancels in the yaw torque
+        DrParams p;
+        p.dt = dr_draw(cfg.sim_dt, f, un[14]);
+        p.mass = dr_draw(0.030f, f, un[15]);
+        p.J[0] = dr_draw(1.33e-5f, f, un[16]);
+        p.J[1] = dr_draw(1.33e-5f, f, un[17]);
+        p.J[2] = dr_draw(2.64e-5f, f, un[18]);
+        p.ftf1 = dr_draw(5.96e-3f, f, un[20]);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             float mtc = dr_draw(cfg.motor_tc, f, un[21 + i]);
             float t2w = dr_draw(1.8f, f, un[25 + i]);
-            float T = fmaxf(mtc, e.dt);
-            e.B[i] = e.dt / T;
-            e.K[i] = 0.028f * 9.81f * t2w / 4.0f;       // agents.py:224 (0.028 kg, not the URDF mass)
+            float T = fmaxf(mtc, p.dt);
+            p.B[i] = p.dt / T;
+            p.K[i] = 0.028f * 9.81f * t2w / 4.0f;           // agents.py:224 (0.028 kg, not the URDF mass)
         }
+        p.store(g);
     }
-    // gyro_lpf.set(stale rpy_dot), base.py:444
-#pragma unroll
-    for (int i = 0; i < 3; ++i) e.lpf[i] = stale_wb[i];
-    // two compute_observation() calls: base.py:453 and, via compute_history, :308
-    const float* la = e.ring + 4;                           // view of action_buffer[-1,:], agents.py:386
-    float rpy_t[3], wb[3];
-    body_rates(e, rpy_t, wb);
+    // gyro_lpf.set(stale rpy_dot), base.py:444; two compute_observation() calls: base.py:453 and, via
+    // compute_history, :308
+    float hist[OD];
+    float ob[13];
     if (NOISE) {
-        float ob[13];
-        observe_full(e, cfg, rpy_t, wb, nz + 12, un + 29, ob);
+        float bias[3], lpf[3] = {stale_wb[0], stale_wb[1], stale_wb[2]}, rpy_t[3];
+        e.get3(CF_S_GYRO_BIAS, bias);
+        quat_to_rpy_bullet(quat, rpy_t);
+        observe_full(pos, vel, rpy_t, wb, bias, lpf, cfg, nz + 12, un + 29, ob);
 #pragma unroll
-        for (int i = 0; i < 13; ++i) obs[i] = ob[i];
-        observe_full(e, cfg, rpy_t, wb, nz + 30, un + 35, ob);
+        for (int i = 0; i < 13; ++i) hist[i] = ob[i];
+        observe_full(pos, vel, rpy_t, wb, bias, lpf, cfg, nz + 30, un + 35, ob);
+        e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
 #pragma unroll
-        for (int i = 0; i < 13; ++i) { obs[17 + i] = ob[i]; e.obs_prev[i] = ob[i]; }
+        for (int i = 0; i < 13; ++i) hist[17 + i] = ob[i];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { obs[13 + i] = la[i]; obs[30 + i] = la[i]; }
+        for (int i = 0; i < 4; ++i) { hist[13 + i] = la[i]; hist[30 + i] = la[i]; }
     } else {
+        e.set3(CF_S_LPF, stale_wb);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { ob[i] = pos[i]; ob[7 + i] = vel[i]; ob[10 + i] = wb[i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ob[3 + i] = quat[i];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            float* o = obs + 21 * h;
 #pragma unroll
-            for (int i = 0; i < 3; ++i) { o[i] = e.pos[i]; o[7 + i] = e.vel[i]; o[10 + i] = wb[i]; }
+            for (int i = 0; i < 13; ++i) hist[21 * h + i] = ob[i];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { o[3 + i] = e.quat[i]; o[13 + i] = la[i]; o[17 + i] = la[i]; }
+            for (int i = 0; i < 4; ++i) { hist[21 * h + 13 + i] = la[i]; hist[21 * h + 17 + i] = la[i]; }
         }
-#pragma unroll
-        for (int i = 0; i < 3; ++i) { e.obs_prev[i] = e.pos[i]; e.obs_prev[7 + i] = e.vel[i]; e.obs_prev[10 + i] = wb[i]; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) e.obs_prev[3 + i] = e.quat[i];
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { e.ap1[i] = la[i]; e.ap2[i] = la[i]; }
-    // Boltzmann() at the end of reset, hover_free.py:536: cdf.searchsorted(u, side='right')
+    for (int i = 0; i < 13; ++i) e.f(CF_S_OBS_PREV + i, ob[i]);
+    e.set4(CF_S_ACT_PREV1, la); e.set4(CF_S_ACT_PREV2, la);
+    store_row<OD>(row, hist);
+    // Boltzmann() at the end of reset, hover_free.py:536: cdf.searchsorted(u, side='right') =
+    // #{k : cdf[k] <= u}; for a float32 u that is #{k : u >= boltz_thr[k]} with boltz_thr[k] the smallest
+    // float32 >= cdf[k] (derived on the host)
     if (cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) {
+        const float u = un[41];
         int k = 0;
-        double u = (double)un[41];
-        while (k < 20 && c_boltz_cdf[k] <= u) ++k;
+#pragma unroll
+        for (int j = 0; j < 20; ++j) k += (u >= cfg.boltz_thr[j]) ? 1 : 0;
         level = k;
     }
-    e.misc = misc_pack(level, 0, 0, false);
+    e.u(CF_S_MISC, misc_pack(level, 0, 0, false));
 }
 
 // ---------------------------------------------------------------------------------- step
 struct StepOut {
-    float rew, cost;
-    int done, truncated;
+    float rew, cost, ep_ret;
+    int done, truncated, ep_len;
 };
 
 // step(): hover_free.py:391-444 / 608-665 / 778-833 (hover.py twins) under gym TimeLimit.
 // Draw slots: z[0:4] OU substep 1, z[4:13] gyro after substep 1, z[13:17] OU substep 2,
 // z[17:26] gyro after substep 2, z[26:44] the full compute_observation of compute_history;
 // u[0:6] its position / attitude uniforms, u[6:8] the random-box disturbance.
-// hist: obs_dim floats = [o(k-1), u(k-2), o(k), u(k-1)] (base.py:305-321).  No reset here.
+// row: obs_dim floats = [o(k-1), u(k-2), o(k), u(k-1)] (base.py:305-321).  No reset here.
+// e: dynamic words (shared memory in the step kernel); p: the env's domain-randomised parameters.
 template <bool NOISE, int HJ_MODE>
-__device__ __forceinline__ StepOut step_env(Env& e, const DevCfg& cfg, const DevTables& tab, const float a[4],
-                                            const Draws<CF_STEP_NORMALS, CF_STEP_UNIFORMS>& dw, float* hist) {
-    const float* nz = dw.z;
-    const float* un = dw.u;
-    e.rng_ctr += 1u;
-    // disturbance, once per control step
-    float d[2] = {0.0f, 0.0f};
-    if (cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) {
-        int level = misc_level(e.misc);
-        if (level > 0) hj_disturbance<HJ_MODE>(e, tab, level, d, nullptr);
-    } else if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {       // dstb_space.sample(), hover_free.py:868-878
-        d[0] = unif(-1e-3f, 1e-3f, un[6]);
-        d[1] = unif(-1e-3f, 1e-3f, un[7]);
+__device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, const DevCfg& cfg, const DevTables& tab,
+                                            const float* thr, const float a[4], const DrawSrc& dw, float* row) {
+    constexpr int OD = NOISE ? 34 : 42;
+    const uint32_t misc = e.u(CF_S_MISC);
+    const int ep_len = (int)e.u(CF_S_EP_LEN);
+    Body b;
+    e.get4(CF_S_QUAT, b.quat); e.get3(CF_S_OMEGA_W, b.ow);
+    // disturbance, once per control step: start the table gather first, the motor model hides its latency
+    int bits = 0;
+    const int level = misc_level(misc);
+    const bool hj = (cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0;
+    if (hj) bits = hj_disturbance_bits<HJ_MODE>(b.quat, b.ow, cfg, tab, thr, level);
+    float d0 = 0.0f, d1 = 0.0f;
+    if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {                // dstb_space.sample(), hover_free.py:868-878
+        float4 ub = dw.u(cfg, 1);
+        d0 = unif(-1e-3f, 1e-3f, ub.z);
+        d1 = unif(-1e-3f, 1e-3f, ub.w);
     }
-    float rpy[3], wb[3];
+    e.get3(CF_S_POS, b.pos); e.get3(CF_S_VEL, b.vel); e.get4(CF_S_MOTOR_X, b.x); e.get4(CF_S_OU, b.ou);
+    // latency ring (agents.py:268-276): substep 1 reads slot ring_idx, substep 2 the other one; both
+    // are overwritten with the new action and ring_idx returns to its value
+    const int ridx = misc_ring(misc) & 1;
+    float del1[4], del2[4];
+    e.get4(CF_S_RING + 4 * ridx, del1); e.get4(CF_S_RING + 4 * (ridx ^ 1), del2);
+    const float invJ[3] = {frcp(p.J[0]), frcp(p.J[1]), frcp(p.J[2])};
+    const float invm = frcp(p.mass);
+    float bias[3], lpf[3];
+    if (NOISE) { e.get3(CF_S_GYRO_BIAS, bias); e.get3(CF_S_LPF, lpf); }
+    float4 zq = dw.z(cfg, 0);
+    if (hj) {
+        float dmax = ((float)level / 10.0f) * 5.3e-3f;      // distur_gener.py:152,160
+        d0 = (bits & 1) ? -dmax : dmax;
+        d1 = (bits & 2) ? -dmax : dmax;
+    }
     // substeps; the reference calls compute_observation() after each (base.py:494-501): only its
     // gyro sample survives (bias walk + low-pass), the rest of that call is overwritten below
-    physics_substep(e, cfg, a, d, nz + 0);
-    if (NOISE) { body_rates(e, rpy, wb); gyro_update(e, cfg, wb, nz + 4, nz + 7, nz + 10); }
-    physics_substep(e, cfg, a, d, nz + 13);
-    body_rates(e, rpy, wb);
-    if (NOISE) gyro_update(e, cfg, wb, nz + 17, nz + 20, nz + 23);
-    // compute_history, base.py:305-321
-    // action history with the reference's aliased view of action_buffer[-1,:] in the first two
-    // steps of an episode (agents.py:386, base.py:459-460): [a,a] then [a,u(k-1)] then normal
-    const bool first = e.ep_len == 0, second = e.ep_len == 1;
-    float h0[4], h1[4];
+    {
+        const float zou[4] = {zq.x, zq.y, zq.z, zq.w};
+        physics_substep(b, p, invJ, invm, cfg, del1, d0, d1, zou);
+    }
+    float R[9], wb[3];
+    float4 z3;
+    if (NOISE) {
+        float4 z1 = dw.z(cfg, 1), z2 = dw.z(cfg, 2);
+        z3 = dw.z(cfg, 3);
+        quat_to_R(b.quat, R); matTvec(R, b.ow, wb);
+        const float zb[3] = {z1.x, z1.y, z1.z}, zr[3] = {z1.w, z2.x, z2.y}, zt[3] = {z2.z, z2.w, z3.x};
+        gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
+    } else {
+        z3 = dw.z(cfg, 3);
+    }
+    float4 z4 = dw.z(cfg, 4);
+    {
+        const float zou[4] = {z3.y, z3.z, z3.w, z4.x};
+        physics_substep(b, p, invJ, invm, cfg, del2, d0, d1, zou);
+    }
+    // final rigid-body state back to the tile; true attitude and body rates (agents.py:434-453)
+    e.set3(CF_S_POS, b.pos); e.set4(CF_S_QUAT, b.quat); e.set3(CF_S_VEL, b.vel); e.set3(CF_S_OMEGA_W, b.ow);
+    e.set4(CF_S_MOTOR_X, b.x); e.set4(CF_S_OU, b.ou);
+    e.set4(CF_S_RING, a); e.set4(CF_S_RING + 4, a);
+    float rpy[3];
+    quat_to_rpy_bullet(b.quat, rpy);
+    quat_to_R(b.quat, R); matTvec(R, b.ow, wb);
+    // compute_history, base.py:305-321.  Action history with the reference's aliased view of
+    // action_buffer[-1,:] in the first two steps of an episode (agents.py:386, base.py:459-460):
+    // [a,a] then [a,u(k-1)] then normal
+    const bool first = ep_len == 0, second = ep_len == 1;
+    float ap1[4], ap2[4], h0[4], h1[4];
+    e.get4(CF_S_ACT_PREV1, ap1); e.get4(CF_S_ACT_PREV2, ap2);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        h0[i] = (first || second) ? e.ring[4 + i] : e.ap2[i];
-        h1[i] = first ? e.ring[4 + i] : e.ap1[i];
+        h0[i] = (first || second) ? a[i] : ap2[i];
+        h1[i] = first ? a[i] : ap1[i];
     }
-    if (NOISE) {
-        float on[13];
-        observe_full(e, cfg, rpy, wb, nz + 26, un, on);
+    e.set4(CF_S_ACT_PREV2, ap1); e.set4(CF_S_ACT_PREV1, a);
+    float hist[OD];
 #pragma unroll
-        for (int i = 0; i < 13; ++i) { hist[i] = e.obs_prev[i]; hist[17 + i] = on[i]; e.obs_prev[i] = on[i]; }
+    for (int i = 0; i < 13; ++i) hist[i] = e.f(CF_S_OBS_PREV + i);
+    if (NOISE) {
+        float4 z5 = dw.z(cfg, 5), z6 = dw.z(cfg, 6);
+        {
+            const float zb[3] = {z4.y, z4.z, z4.w}, zr[3] = {z5.x, z5.y, z5.z}, zt[3] = {z5.w, z6.x, z6.y};
+            gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
+        }
+        float4 z7 = dw.z(cfg, 7), z8 = dw.z(cfg, 8), z9 = dw.z(cfg, 9), z10 = dw.z(cfg, 10), u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
+        const float z[18] = {z6.z, z6.w, z7.x, z7.y, z7.z, z7.w, z8.x, z8.y, z8.z, z8.w, z9.x, z9.y, z9.z, z9.w,
+                             z10.x, z10.y, z10.z, z10.w};
+        const float u[6] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y};
+        float on[13];
+        observe_full(b.pos, b.vel, rpy, wb, bias, lpf, cfg, z, u, on);
+        e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
+#pragma unroll
+        for (int i = 0; i < 13; ++i) { hist[17 + i] = on[i]; e.f(CF_S_OBS_PREV + i, on[i]); }
 #pragma unroll
         for (int i = 0; i < 4; ++i) { hist[13 + i] = h0[i]; hist[30 + i] = h1[i]; }
     } else {
 #pragma unroll
-        for (int i = 0; i < 13; ++i) hist[i] = e.obs_prev[i];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { hist[13 + i] = e.ap1[i]; hist[17 + i] = h0[i]; hist[38 + i] = h1[i]; hist[34 + i] = a[i]; }
+        for (int i = 0; i < 4; ++i) { hist[13 + i] = ap1[i]; hist[17 + i] = h0[i]; hist[38 + i] = h1[i]; hist[34 + i] = a[i]; }
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            hist[21 + i] = e.pos[i]; hist[28 + i] = e.vel[i]; hist[31 + i] = wb[i];
-            e.obs_prev[i] = e.pos[i]; e.obs_prev[7 + i] = e.vel[i]; e.obs_prev[10 + i] = wb[i];
+            hist[21 + i] = b.pos[i]; hist[28 + i] = b.vel[i]; hist[31 + i] = wb[i];
+            e.f(CF_S_OBS_PREV + i, b.pos[i]); e.f(CF_S_OBS_PREV + 7 + i, b.vel[i]); e.f(CF_S_OBS_PREV + 10 + i, wb[i]);
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { hist[24 + i] = e.quat[i]; e.obs_prev[3 + i] = e.quat[i]; }
+        for (int i = 0; i < 4; ++i) { hist[24 + i] = b.quat[i]; e.f(CF_S_OBS_PREV + 3 + i, b.quat[i]); }
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) { e.ap2[i] = e.ap1[i]; e.ap1[i] = a[i]; }
+    store_row<OD>(row, hist);
     // compute_done (hover_free.py:449-461), reward (hover_free.py:206-235 / hover.py:184-202),
     // cost (hover_free.py:138-166) on the TRUE state
-    bool dn = e.pos[2] < 0.2f;
+    bool dn = b.pos[2] < 0.2f;
     dn |= fabsf(rpy[0]) > cfg.done_rp_rad || fabsf(rpy[1]) > cfg.done_rp_rad;
 #pragma unroll
     for (int i = 0; i < 3; ++i) dn |= (180.0f * fabsf(wb[i]) / kPi) > cfg.done_rate_deg;
     float nca = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { float c = 0.5f * (fminf(1.0f, fmaxf(-1.0f, a[i])) + 1.0f); nca += c * c; }
-    float p_action = cfg.pen_action * sqrtf(nca);
-    float p_rpy = cfg.pen_angle * sqrtf(rpy[0] * rpy[0] + rpy[1] * rpy[1] + rpy[2] * rpy[2]);
-    float p_spin = cfg.pen_spin * sqrtf(wb[0] * wb[0] + wb[1] * wb[1] + wb[2] * wb[2]);
+    for (int i = 0; i < 4; ++i) { float c = 0.5f * (clampf(a[i], -1.0f, 1.0f) + 1.0f); nca += c * c; }
+    float p_action = cfg.pen_action * fsqrt(nca);
+    float p_rpy = cfg.pen_angle * fsqrt(rpy[0] * rpy[0] + rpy[1] * rpy[1] + rpy[2] * rpy[2]);
+    float p_spin = cfg.pen_spin * fsqrt(wb[0] * wb[0] + wb[1] * wb[1] + wb[2] * wb[2]);
     float p_term = dn ? cfg.pen_terminal : 0.0f;
-    float p_vel = cfg.pen_velocity * sqrtf(e.vel[0] * e.vel[0] + e.vel[1] * e.vel[1] + e.vel[2] * e.vel[2]);
+    float p_vel = cfg.pen_velocity * fsqrt(b.vel[0] * b.vel[0] + b.vel[1] * b.vel[1] + b.vel[2] * b.vel[2]);
     float penalties = (((p_rpy + p_spin) + p_vel) + p_action) + p_term;
     float r;
     if (cfg.reward_kind == CF_REWARD_FREE) {
-        r = -penalties - cfg.pen_z * fabsf(e.pos[2] - 1.0f);
+        r = -penalties - cfg.pen_z * fabsf(b.pos[2] - 1.0f);
     } else {
-        float dx = e.pos[0], dy = e.pos[1], dz = e.pos[2] - 1.0f;
-        r = -sqrtf(dx * dx + dy * dy + dz * dz) - penalties;
+        float dx = b.pos[0], dy = b.pos[1], dz = b.pos[2] - 1.0f;
+        r = -fsqrt(dx * dx + dy * dy + dz * dz) - penalties;
     }
     const float kDeg10 = 10.0f * kPi / 180.0f;
-    bool c = fabsf(e.pos[0]) > 0.10f || fabsf(e.pos[1]) > 0.10f || e.pos[2] > 1.20f;
+    bool c = fabsf(b.pos[0]) > 0.10f || fabsf(b.pos[1]) > 0.10f || b.pos[2] > 1.20f;
     c |= fabsf(rpy[0]) > kDeg10 || fabsf(rpy[1]) > kDeg10;
 #pragma unroll
     for (int i = 0; i < 3; ++i) c |= fabsf(wb[i]) > 0.25f || fabsf(a[i]) > cfg.cost_rate_limit;   // mislabelled slices, :155-160
-    e.ep_len += 1; e.ep_ret += r;
     StepOut o;
+    o.ep_len = ep_len + 1;
+    o.ep_ret = e.f(CF_S_EP_RET) + r;
+    e.u(CF_S_EP_LEN, (uint32_t)o.ep_len); e.f(CF_S_EP_RET, o.ep_ret);
     o.truncated = 0;
-    if (cfg.max_ep_steps > 0 && e.ep_len >= cfg.max_ep_steps) { o.truncated = dn ? 0 : 1; dn = true; }
+    if (cfg.max_ep_steps > 0 && o.ep_len >= cfg.max_ep_steps) { o.truncated = dn ? 0 : 1; dn = true; }
     o.rew = r; o.cost = c ? 1.0f : 0.0f; o.done = dn ? 1 : 0;
     return o;
 }

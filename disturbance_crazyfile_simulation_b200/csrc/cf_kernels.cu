@@ -1,104 +1,217 @@
 // cf_kernels.cu - kernels of the batched CrazyFlie hover environment and their launchers (sm_100a).
 //
-// Layout in HBM: per handle one float4 array S[19][n_envs] (structure-of-arrays in 128-bit
-// groups, see cf_device.cuh), HJ tables (fp32 value tables and/or packed 2-bit sign tables),
-// and caller-owned env-major I/O rows act[n][4], obs[n][obs_dim], rew[n], done[n], cost[n].
-// One thread per env; no inter-thread communication on the step path.
+// Layout in HBM: per handle one float array S[n_tiles][76][CF_TILE] (word-major tiles of CF_TILE
+// envs, see cf_device.cuh), the HJ tables (packed 2-bit sign tables in one slab and/or fp32 value
+// tables), and caller-owned env-major I/O rows act[n][4], obs[n][obs_dim], rew[n], done[n], cost[n].
+//
+// Step kernel: one CTA per tile, one thread per env.  The 60 dynamic state words of the tile
+// (30 KB, contiguous) arrive in shared memory with ONE bulk async copy (cp.async.bulk + mbarrier,
+// SASS UBLKCP) while the threads fetch their action and domain-randomised parameters; the step
+// runs against shared memory (conflict-free word-major accesses), the observation rows are
+// assembled in shared memory, and the tile's new state (30 KB) and observation rows (17 KB) leave
+// with one bulk copy each.  No inter-thread communication on the step path.
 #include "cf_device.cuh"
 #include "cf_kernels.h"
 
 namespace cf {
 
-// obs rows are 136 B (34 floats) or 168 B (42 floats): 8-byte aligned -> 64-bit stores
-template <int DIM>
-__device__ __forceinline__ void store_row(float* __restrict__ dst, const float* v) {
-    float2* p = reinterpret_cast<float2*>(dst);
-#pragma unroll
-    for (int k = 0; k < DIM / 2; ++k) p[k] = make_float2(v[2 * k], v[2 * k + 1]);
+// ---------------------------------------------------------------------------------- bulk-copy PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-
-__global__ void k_init(float4* __restrict__ S, int n, DevCfg cfg) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    Env e;
-    init_env(e, cfg);
-    store_env(e, S, n, i);
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-
-// constructor-time compute_observation() (base.py:141): gyro_bias <- sigma_b * N(0,1), event tag 3
-__device__ __forceinline__ void consume_fresh(Env& e, const DevCfg& cfg, long long gid, bool noise) {
-    if (!misc_fresh(e.misc)) return;
-    if (noise && !cfg.injected) {
-        Rng rng = make_rng(cfg, gid, 0u, 3u);
-        float4 z = rng.normals(0);
-        e.bias[0] = cfg.gyro_sb * z.x; e.bias[1] = cfg.gyro_sb * z.y; e.bias[2] = cfg.gyro_sb * z.z;
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
     }
-    e.misc &= 0x7fffffffu;
+}
+// global -> shared, completion counted in bytes on the mbarrier (16-byte aligned, 16-byte multiple)
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// shared -> global, tracked by the thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// make generic-proxy shared-memory writes visible to the async proxy (before a bulk store reads them)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory"); return t; }
+__device__ __forceinline__ unsigned smid() { unsigned r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
+
+// ---------------------------------------------------------------------------------- kernels
+// all envs of the padded tile array get a valid constructor state
+__global__ void k_init(float* __restrict__ S, int n_pad, DevCfg cfg) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    init_env(EnvRef{env_global(S, i)}, cfg);
 }
 
 template <bool NOISE>
-__global__ void __launch_bounds__(128) k_reset(float4* __restrict__ S, int n, DevCfg cfg, const uint8_t* __restrict__ mask,
-                                              float* __restrict__ obs, const float* inj_z, const float* inj_u) {
+__global__ void __launch_bounds__(128) k_reset(float* __restrict__ S, int n, const __grid_constant__ DevCfg cfg,
+                                              const uint8_t* __restrict__ mask, float* __restrict__ obs,
+                                              const float* inj_z, const float* inj_u) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     if (mask && !mask[i]) return;
     constexpr int OD = NOISE ? 34 : 42;
-    Env e;
-    load_env(e, S, n, i);
+    const EnvRef g{env_global(S, i)};
     long long gid = cfg.gid_base + i;
-    consume_fresh(e, cfg, gid, NOISE);
-    Draws<CF_RESET_NORMALS, CF_RESET_UNIFORMS> dw;
-    if (cfg.injected) dw.load(inj_z, inj_u, n, i);
-    else { dw.generate(make_rng(cfg, gid, e.rng_ctr, 2u)); e.rng_ctr += 1u; }
-    float o[OD];
-    reset_env<NOISE>(e, cfg, dw, o);
-    store_env(e, S, n, i);
-    store_row<OD>(obs + (size_t)i * OD, o);
+    consume_fresh(g, cfg, gid, NOISE);
+    uint32_t ctr = g.u(CF_S_RNG_CTR);
+    if (!cfg.injected) g.u(CF_S_RNG_CTR, ctr + 1u);
+    DrawSrc dw = make_draws(cfg, gid, ctr, 2u, inj_z, inj_u, n, i, CF_RESET_UNIFORMS);
+    float z[CF_RESET_NORMALS], u[(CF_RESET_UNIFORMS + 3) / 4 * 4];
+    reset_draws(dw, cfg, z, u);
+    reset_env<NOISE>(g, g, cfg, z, u, obs + (size_t)i * OD);
 }
 
-// env.step for all envs, `k` control steps per launch with the state held in registers.
+template <int OD>
+__device__ __forceinline__ void copy_row(float* __restrict__ dst, const float* src) {
+    float2* d = reinterpret_cast<float2*>(dst);
+    const float2* s = reinterpret_cast<const float2*>(src);
+#pragma unroll
+    for (int j = 0; j < OD / 2; ++j) d[j] = s[j];
+}
+
+#ifndef CF_MIN_CTAS
+#define CF_MIN_CTAS (512 / CF_TILE)      /* 512 threads / SM at <= 128 registers: 65 536 envs fit in one wave */
+#endif
+
+// env.step for all envs, `k` control steps per launch with the tile's state held in shared memory.
+// Envs that finish an episode are reset in place after the tile's step phase: the CTA's warps share
+// the tile's finished envs; for each, 23 lanes produce the 23 Philox blocks of the reset event in
+// parallel into shared memory and lane 0 runs the (short) serial part - the reset leaves the
+// critical path of the warp that happened to own the env.
 template <bool NOISE, int HJ_MODE>
-__global__ void __launch_bounds__(128) k_step(float4* __restrict__ S, int n, int k, DevCfg cfg, DevTables tab, StepIO io) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+__global__ void __launch_bounds__(CF_TILE, CF_MIN_CTAS)
+k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, const __grid_constant__ DevTables tab,
+       const __grid_constant__ StepIO io) {
     constexpr int OD = NOISE ? 34 : 42;
-    Env e;
-    load_env(e, S, n, i);
-    long long gid = cfg.gid_base + i;
-    consume_fresh(e, cfg, gid, NOISE);
-    for (int t = 0; t < k; ++t) {
-        size_t row = (size_t)t * n + i;
-        float4 av = *reinterpret_cast<const float4*>(io.act + row * 4);
-        float a[4] = {av.x, av.y, av.z, av.w};
-        float hist[OD];
-        StepOut so;
-        {
-            Draws<CF_STEP_NORMALS, CF_STEP_UNIFORMS> dw;
-            if (cfg.injected) dw.load(io.inj_step_z, io.inj_step_u, n, i);
-            else dw.generate(make_rng(cfg, gid, e.rng_ctr, 0u));
-            so = step_env<NOISE, HJ_MODE>(e, cfg, tab, a, dw, hist);
-        }
-        io.rew[row] = so.rew;
-        io.done[row] = (uint8_t)so.done;
-        if (io.cost) io.cost[row] = so.cost;
-        if (io.truncated) io.truncated[i] = (uint8_t)so.truncated;
-        if (so.done) {
-            io.fin_ret[i] = e.ep_ret;
-            io.fin_len[i] = e.ep_len;
-            atomicAdd(io.agg + 0, 1.0);
-            atomicAdd(io.agg + 1, (double)e.ep_ret);
-            atomicAdd(io.agg + 2, (double)e.ep_len);
-        }
-        if (so.done && cfg.auto_reset) {
-            if (io.term_obs) store_row<OD>(io.term_obs + (size_t)i * OD, hist);
-            Draws<CF_RESET_NORMALS, CF_RESET_UNIFORMS> dr;
-            if (cfg.injected) dr.load(io.inj_reset_z, io.inj_reset_u, n, i);
-            else dr.generate(make_rng(cfg, gid, e.rng_ctr, 1u));
-            reset_env<NOISE>(e, cfg, dr, hist);
-        }
-        store_row<OD>(io.obs + row * OD, hist);
+    constexpr int NW = CF_TILE / 32;
+    constexpr uint32_t kStateBytes = CF_DYN_WORDS * CF_TILE * 4, kObsBytes = OD * CF_TILE * 4;
+    extern __shared__ __align__(128) float smem[];
+    float* s_state = smem;                                  // [60][CF_TILE]
+    float* s_obs = s_state + CF_DYN_WORDS * CF_TILE;        // [CF_TILE][OD]
+    float* s_thr = s_obs + OD * CF_TILE;                    // [6][16]
+    float* s_draw = s_thr + 96;                             // [NW][96] reset draws of the env a warp is resetting
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_draw + NW * 96);
+    int* s_ndone = reinterpret_cast<int*>(mbar + 1);        // [2]
+    uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x, i = tile * CF_TILE + tid;
+    float* gtile = S + (size_t)tile * (CF_STATE_WORDS * CF_TILE);
+    const bool valid = i < n;
+    const bool bulk_obs = io.bulk_obs && (tile + 1) * CF_TILE <= n;
+    unsigned long long* tr = io.trace ? io.trace + CF_TRACE_WORDS * (size_t)tile : nullptr;    // per-CTA timeline (debug)
+    if (tr && tid == 0) { tr[0] = smid(); tr[1] = gtimer(); }
+    if (tid == 0) {
+        s_ndone[0] = 0;
+        mbar_init(mbar, 1);
+        mbar_arrive_expect_tx(mbar, kStateBytes);
+        bulk_g2s(s_state, gtile, kStateBytes, mbar);
     }
-    store_env(e, S, n, i);
+    if (tid < 96) s_thr[tid] = __ldg(tab.thr + tid);
+    const EnvRef e{s_state + tid};
+    const EnvRef g{gtile + tid};
+    DrParams p;
+    p.load(g);                                              // coalesced loads, in flight with the bulk copy
+    float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) av = __ldg(reinterpret_cast<const float4*>(io.act) + i);
+    const long long gid = cfg.gid_base + i;
+    float* row = s_obs + tid * OD;
+    __syncthreads();                                        // mbarrier initialised, thresholds in place
+    mbar_wait(mbar, 0);
+    if (tr && tid == 0) tr[2] = gtimer();
+    if (valid) consume_fresh(e, cfg, gid, NOISE);
+    int total_done = 0;
+    for (int t = 0; t < k; ++t) {
+        const size_t r = (size_t)t * n + i;
+        bool my_reset = false;
+        if (valid) {
+            if (t > 0) av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
+            const float a[4] = {av.x, av.y, av.z, av.w};
+            const uint32_t ctr = e.u(CF_S_RNG_CTR);          // step event: counter before the increment, tag 0;
+            e.u(CF_S_RNG_CTR, ctr + 1u);                    // an in-place reset in this launch: counter after it, tag 1
+            const DrawSrc dw = make_draws(cfg, gid, ctr, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
+            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, s_thr, a, dw, row);
+            io.rew[r] = so.rew;
+            io.done[r] = (uint8_t)so.done;
+            if (io.cost) io.cost[r] = so.cost;
+            if (io.truncated) io.truncated[i] = (uint8_t)so.truncated;
+            if (so.done) {
+                io.fin_ret[i] = so.ep_ret;
+                io.fin_len[i] = so.ep_len;
+                double* agg = io.agg + 4 * (tile % CF_AGG_SLOTS);
+                atomicAdd(agg + 0, 1.0);
+                atomicAdd(agg + 1, (double)so.ep_ret);
+                atomicAdd(agg + 2, (double)so.ep_len);
+                if (cfg.auto_reset) {
+                    if (io.term_obs) copy_row<OD>(io.term_obs + (size_t)i * OD, row);
+                    s_list[atomicAdd(s_ndone, 1)] = (uint8_t)tid;
+                    my_reset = true;
+                }
+            }
+        }
+        if (tr && t == 0) { __syncwarp(); if (lane == 0) tr[3 + warp] = gtimer(); }
+        fence_async_smem();
+        __syncthreads();                                    // step phase of the tile complete, list of finished envs final
+        if (tr && tid == 0 && t == 0) tr[7] = gtimer();
+        const int nd = s_ndone[0];
+        if (nd > 0) {                                       // uniform over the CTA
+            for (int j = warp; j < nd; j += NW) {
+                const int et = s_list[j];
+                const EnvRef ee{s_state + et};
+                const EnvRef gg{gtile + et};
+                float* zs = s_draw + warp * 96;
+                float* us = zs + CF_RESET_NORMALS;
+                const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
+                                              io.inj_reset_u, n, tile * CF_TILE + et, CF_RESET_UNIFORMS);
+                if (lane < 12) {
+                    float4 v = dr.z(cfg, lane);
+                    zs[4 * lane] = v.x; zs[4 * lane + 1] = v.y; zs[4 * lane + 2] = v.z; zs[4 * lane + 3] = v.w;
+                } else if (lane < 23) {
+                    float4 v = dr.u(cfg, lane - 12);
+                    us[4 * (lane - 12)] = v.x; us[4 * (lane - 12) + 1] = v.y; us[4 * (lane - 12) + 2] = v.z; us[4 * (lane - 12) + 3] = v.w;
+                }
+                __syncwarp();
+                if (lane == 0) reset_env<NOISE>(ee, gg, cfg, zs, us, s_obs + et * OD);
+                __syncwarp();
+            }
+            total_done += nd;
+            fence_async_smem();
+            __syncthreads();                                // resets complete
+            if (tid == 0) s_ndone[0] = 0;
+            if (my_reset && t + 1 < k) p.load(g);
+        }
+        if (tr && tid == 0 && t == 0) tr[8] = gtimer();
+        if (bulk_obs) {
+            if (tid == 0) {
+                bulk_s2g(io.obs + ((size_t)t * n + (size_t)tile * CF_TILE) * OD, s_obs, kObsBytes);
+                if (t + 1 == k) bulk_s2g(gtile, s_state, kStateBytes);
+                bulk_commit();
+                bulk_wait_read();                           // shared memory is free again / may be released
+            }
+        } else {
+            if (valid) copy_row<OD>(io.obs + r * OD, row);
+            if (t + 1 == k && tid == 0) {
+                bulk_s2g(gtile, s_state, kStateBytes);
+                bulk_commit();
+                bulk_wait_read();
+            }
+        }
+        if (t + 1 < k) __syncthreads();                     // rows may be overwritten by the next step
+    }
+    if (tr && tid == 0) { tr[9] = gtimer(); tr[10] = (unsigned long long)total_done; }
 }
 
 // Packed 2-bit sign table of one level from its fp32 value table, with the reference's own
@@ -118,7 +231,7 @@ __global__ void k_hj_signs(const float* __restrict__ V, uint8_t* __restrict__ P,
     P[b] = (uint8_t)out;
 }
 
-// Grid.get_index + sign lookup for given float64 (roll,pitch,yaw,p,q,r) states
+// Grid.get_index + sign lookup for given float64 (roll,pitch,yaw,p,q,r) states (the float64 rule)
 __global__ void k_hj_lookup(const double* __restrict__ states, int n, const float* V, const uint8_t* P,
                             int* __restrict__ idx_out, float* __restrict__ sign_out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -130,25 +243,37 @@ __global__ void k_hj_lookup(const double* __restrict__ states, int n, const floa
     sign_out[2 * (size_t)i] = (bits & 1) ? -1.0f : 1.0f;
     sign_out[2 * (size_t)i + 1] = (bits & 2) ? -1.0f : 1.0f;
 }
+// the same for float32 states through the step kernel's own float32 threshold rule
+__global__ void k_hj_lookup_f32(const float* __restrict__ states, int n, const __grid_constant__ DevCfg cfg, const float* V,
+                                const uint8_t* P, const float* __restrict__ thr, int* __restrict__ idx_out,
+                                float* __restrict__ sign_out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int idx[6];
+#pragma unroll
+    for (int d = 0; d < 6; ++d) { idx[d] = hj_index_f32(states[(size_t)i * 6 + d], d, thr, cfg); idx_out[(size_t)i * 6 + d] = idx[d]; }
+    int bits = P ? hj_signbits_packed(P, idx) : hj_signbits_value(V, idx);
+    sign_out[2 * (size_t)i] = (bits & 1) ? -1.0f : 1.0f;
+    sign_out[2 * (size_t)i + 1] = (bits & 2) ? -1.0f : 1.0f;
+}
 
-// env-major host record <-> device SoA groups
-__global__ void k_unpack_state(const float4* __restrict__ S, int n, float4* __restrict__ rec) {
+// env-major host record [n][76] <-> tiled device state
+__global__ void k_unpack_state(const float* __restrict__ S, int n, float* __restrict__ rec) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-#pragma unroll
-    for (int g = 0; g < kGroups; ++g) rec[(size_t)i * kGroups + g] = S[(size_t)g * n + i];
+    const float* g = env_global(const_cast<float*>(S), i);
+    for (int w = 0; w < CF_STATE_WORDS; ++w) rec[(size_t)i * CF_STATE_WORDS + w] = g[w * CF_TILE];
 }
-__global__ void k_pack_state(float4* __restrict__ S, int n, const float4* __restrict__ rec) {
+__global__ void k_pack_state(float* __restrict__ S, int n, const float* __restrict__ rec) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-#pragma unroll
-    for (int g = 0; g < kGroups; ++g) S[(size_t)g * n + i] = rec[(size_t)i * kGroups + g];
+    float* g = env_global(S, i);
+    for (int w = 0; w < CF_STATE_WORDS; ++w) g[w * CF_TILE] = rec[(size_t)i * CF_STATE_WORDS + w];
 }
-__global__ void k_levels(const float4* __restrict__ S, int n, float* __restrict__ out) {
+__global__ void k_levels(const float* __restrict__ S, int n, float* __restrict__ out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    float4 g = S[(size_t)(CF_S_MISC / 4) * n + i];
-    out[i] = (float)misc_level(__float_as_uint(g.w)) / 10.0f;
+    out[i] = (float)misc_level(__float_as_uint(env_global(const_cast<float*>(S), i)[CF_S_MISC * CF_TILE])) / 10.0f;
 }
 
 // PPO GAE (Buffer.finish_path, algs/core.py:498-535; discount_cumsum :105-119), time-major
@@ -190,24 +315,43 @@ cudaError_t upload_constants(const double grid[6][CF_HJ_PTS], const double dx[6]
     return cudaMemcpyToSymbol(c_boltz_cdf, cdf, sizeof(double) * 21);
 }
 
-void launch_init(float4* S, int n, const DevCfg& cfg, cudaStream_t st) {
-    k_init<<<blocks_for(n, 128), 128, 0, st>>>(S, n, cfg);
+void launch_init(float* S, int n_pad, const DevCfg& cfg, cudaStream_t st) {
+    k_init<<<blocks_for(n_pad, 128), 128, 0, st>>>(S, n_pad, cfg);
 }
-void launch_reset(float4* S, int n, const DevCfg& cfg, const uint8_t* mask, float* obs, const float* inj_z,
+void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float* obs, const float* inj_z,
                   const float* inj_u, cudaStream_t st) {
     if (cfg.obs_noise) k_reset<true><<<blocks_for(n, 128), 128, 0, st>>>(S, n, cfg, mask, obs, inj_z, inj_u);
     else k_reset<false><<<blocks_for(n, 128), 128, 0, st>>>(S, n, cfg, mask, obs, inj_z, inj_u);
 }
-void launch_step(float4* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st) {
-    dim3 g(blocks_for(n, 128)), b(128);
+
+size_t step_smem_bytes(int obs_dim) {
+    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + (CF_TILE / 32) * 96 * 4 + 8 + 8 + CF_TILE;
+}
+
+template <bool NOISE, int HJ_MODE>
+static cudaError_t launch_step_variant(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io,
+                                       cudaStream_t st) {
+    static bool configured[64] = {};                     // per device: opt in to > 48 KB of dynamic shared memory
+    const size_t smem = step_smem_bytes(NOISE ? 34 : 42);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        cudaError_t err = cudaFuncSetAttribute(k_step<NOISE, HJ_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return err;
+        cudaFuncSetAttribute(k_step<NOISE, HJ_MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured[dev] = true;
+    }
+    k_step<NOISE, HJ_MODE><<<blocks_for(n, CF_TILE), CF_TILE, smem, st>>>(S, n, k, cfg, tab, io);
+    return cudaSuccess;
+}
+cudaError_t launch_step(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st) {
     const bool sign = cfg.hj_mode == CF_HJ_SIGN_TABLE;
     if (cfg.obs_noise) {
-        if (sign) k_step<true, CF_HJ_SIGN_TABLE><<<g, b, 0, st>>>(S, n, k, cfg, tab, io);
-        else k_step<true, CF_HJ_VALUE_TABLE><<<g, b, 0, st>>>(S, n, k, cfg, tab, io);
-    } else {
-        if (sign) k_step<false, CF_HJ_SIGN_TABLE><<<g, b, 0, st>>>(S, n, k, cfg, tab, io);
-        else k_step<false, CF_HJ_VALUE_TABLE><<<g, b, 0, st>>>(S, n, k, cfg, tab, io);
+        if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE>(S, n, k, cfg, tab, io, st);
+        return launch_step_variant<true, CF_HJ_VALUE_TABLE>(S, n, k, cfg, tab, io, st);
     }
+    if (sign) return launch_step_variant<false, CF_HJ_SIGN_TABLE>(S, n, k, cfg, tab, io, st);
+    return launch_step_variant<false, CF_HJ_VALUE_TABLE>(S, n, k, cfg, tab, io, st);
 }
 void launch_hj_signs(const float* V, uint8_t* P, cudaStream_t st) {
     int nb = (CF_HJ_CELLS + 3) / 4;
@@ -217,13 +361,17 @@ void launch_hj_lookup(const double* states, int n, const float* V, const uint8_t
                       cudaStream_t st) {
     k_hj_lookup<<<blocks_for(n, 128), 128, 0, st>>>(states, n, V, P, idx, sign);
 }
-void launch_unpack_state(const float4* S, int n, float4* rec, cudaStream_t st) {
+void launch_hj_lookup_f32(const float* states, int n, const DevCfg& cfg, const float* V, const uint8_t* P, const float* thr,
+                          int* idx, float* sign, cudaStream_t st) {
+    k_hj_lookup_f32<<<blocks_for(n, 128), 128, 0, st>>>(states, n, cfg, V, P, thr, idx, sign);
+}
+void launch_unpack_state(const float* S, int n, float* rec, cudaStream_t st) {
     k_unpack_state<<<blocks_for(n, 128), 128, 0, st>>>(S, n, rec);
 }
-void launch_pack_state(float4* S, int n, const float4* rec, cudaStream_t st) {
+void launch_pack_state(float* S, int n, const float* rec, cudaStream_t st) {
     k_pack_state<<<blocks_for(n, 128), 128, 0, st>>>(S, n, rec);
 }
-void launch_levels(const float4* S, int n, float* out, cudaStream_t st) {
+void launch_levels(const float* S, int n, float* out, cudaStream_t st) {
     k_levels<<<blocks_for(n, 128), 128, 0, st>>>(S, n, out);
 }
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,

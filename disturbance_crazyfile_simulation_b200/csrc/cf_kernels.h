@@ -5,16 +5,19 @@
 namespace cf {
 
 cudaError_t upload_constants(const double grid[6][CF_HJ_PTS], const double dx[6], const double cdf[21]);
-void launch_init(float4* S, int n, const DevCfg& cfg, cudaStream_t st);
-void launch_reset(float4* S, int n, const DevCfg& cfg, const uint8_t* mask, float* obs, const float* inj_z,
+void launch_init(float* S, int n_pad, const DevCfg& cfg, cudaStream_t st);
+void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float* obs, const float* inj_z,
                   const float* inj_u, cudaStream_t st);
-void launch_step(float4* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st);
+cudaError_t launch_step(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st);
+size_t step_smem_bytes(int obs_dim);
 void launch_hj_signs(const float* V, uint8_t* P, cudaStream_t st);
 void launch_hj_lookup(const double* states, int n, const float* V, const uint8_t* P, int* idx, float* sign,
                       cudaStream_t st);
-void launch_unpack_state(const float4* S, int n, float4* rec, cudaStream_t st);
-void launch_pack_state(float4* S, int n, const float4* rec, cudaStream_t st);
-void launch_levels(const float4* S, int n, float* out, cudaStream_t st);
+void launch_hj_lookup_f32(const float* states, int n, const DevCfg& cfg, const float* V, const uint8_t* P, const float* thr,
+                          int* idx, float* sign, cudaStream_t st);
+void launch_unpack_state(const float* S, int n, float* rec, cudaStream_t st);
+void launch_pack_state(float* S, int n, const float* rec, cudaStream_t st);
+void launch_levels(const float* S, int n, float* out, cudaStream_t st);
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int T, int N, float* adv, float* tgt, float* disc_ret,
                 cudaStream_t st);

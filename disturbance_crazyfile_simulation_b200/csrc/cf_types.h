@@ -5,9 +5,24 @@
 
 #include "../../include/cf_abi.h"
 
+// envs per tile = threads per CTA of the step kernel.  State in HBM: float S[n_tiles][CF_STATE_WORDS][CF_TILE]
+#ifndef CF_TILE
+#define CF_TILE 128
+#endif
+// words 0..CF_DYN_WORDS-1 change every step (staged through shared memory by the step kernel);
+// the rest are the domain-randomised parameters, rewritten by reset only
+#define CF_DYN_WORDS CF_S_DT
+// bytes between the packed 2-bit sign tables of consecutive levels (>= ceil(15^6 / 4), 128-B multiple)
+#define CF_SIGN_STRIDE 2847744
+// episode-statistics accumulators are spread over slots (by tile) to avoid same-address atomics
+#define CF_AGG_SLOTS 64
+// uint64 words per tile of the debug timeline (cf_set_trace_buffer)
+#define CF_TRACE_WORDS 16
+
 namespace cf {
 
-constexpr int kGroups = CF_STATE_WORDS / 4;   // 19 float4 groups per env
+static_assert(CF_DYN_WORDS == 60 && CF_STATE_WORDS == 76, "state record layout");
+static_assert((CF_DYN_WORDS * CF_TILE * 4) % 16 == 0, "bulk copies need 16-byte multiples");
 
 // Everything the kernels need from cf_config, pre-derived in float64 on the host (cf_abi.cu).
 struct DevCfg {
@@ -24,14 +39,17 @@ struct DevCfg {
     float gyro_sb, gyro_pi, gyro_rw, gyro_ton;   // sensors.py:121-134 constants at dt = 1/200
     float quat_std, quat_unif;
     float gnd_hclip;
-    uint32_t seed_lo, seed_hi;
+    float hj_lo[6], hj_inv_dx[6];           // grid origin and 1/dx per dim (index guess, float32)
+    float boltz_thr[20];                    // Boltzmann level draw: smallest float32 >= cdf[k] (envs/utils.py:27-39)
+    uint32_t pk[10][2];                     // Philox4x32-10 round keys of the seed
     long long gid_base;
 };
 
-// Device-side tables owned by the handle.
+// Device-side tables owned by the handle (or borrowed from another handle on the same GPU).
 struct DevTables {
-    const float* value[CF_MAX_LEVELS];      // fp32 (15,)*6 value tables (CF_HJ_VALUE_TABLE) or null
-    const uint8_t* signs[CF_MAX_LEVELS];    // packed 2-bit sign tables, 4 cells / byte, or null
+    const float* const* value;              // device array [CF_MAX_LEVELS] of fp32 (15,)*6 value tables (or null entries)
+    const uint8_t* signs;                   // slab [CF_MAX_LEVELS][CF_SIGN_STRIDE]: packed 2-bit sign tables, 4 cells / byte
+    const float* thr;                       // [6][16] float32 index thresholds (cf_device.cuh hj_index_f32)
 };
 
 // Caller-owned I/O of one step launch plus the handle-owned side buffers.
@@ -49,7 +67,9 @@ struct StepIO {
     const float* inj_reset_u;
     float* fin_ret;        // [n] return of the last finished episode
     int* fin_len;          // [n]
-    double* agg;           // [4]: episodes, sum return, sum length, (spare)
+    double* agg;           // [CF_AGG_SLOTS][4]: episodes, sum return, sum length, (spare)
+    int bulk_obs;          // obs rows of a full tile may leave with one bulk copy (16-byte aligned)
+    unsigned long long* trace;   // debug: [n_tiles][CF_TRACE_WORDS] per-CTA timeline (cf_set_trace_buffer) or null
 };
 
 }  // namespace cf

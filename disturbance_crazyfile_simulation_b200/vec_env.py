@@ -227,6 +227,16 @@ class CrazyFlieVecEnv:
                                             idx.ctypes.data_as(C.c_void_p), sign.ctypes.data_as(C.c_void_p)))
         return idx, sign
 
+    def hj_lookup_f32(self, level: float, states: np.ndarray):
+        """The same lookup for float32 states through the step kernel's own float32 threshold rule."""
+        s = np.ascontiguousarray(states, dtype=np.float32)
+        n = s.shape[0]
+        idx = np.empty((n, 6), np.int32)
+        sign = np.empty((n, 2), np.float32)
+        abi.check(self._L.cf_hj_lookup_f32_host(self._h, level_index(level), s.ctypes.data_as(C.c_void_p), n,
+                                                idx.ctypes.data_as(C.c_void_p), sign.ctypes.data_as(C.c_void_p)))
+        return idx, sign
+
     def episode_stats(self, reset: bool = False) -> dict:
         out = (C.c_double * 4)()
         abi.check(self._L.cf_episode_stats(self._h, int(reset), out, None, None))

@@ -152,7 +152,8 @@ int cf_get_hj_signs(cf_env* env, int32_t level_idx, uint8_t* out_host);
  * obs: [n_envs][obs_dim] float32 (rows of unmasked envs untouched). */
 int cf_reset_dev(cf_env* env, const uint8_t* mask, float* obs, void* stream);
 
-/* env.step(action) under TimeLimit for all envs.  act [n][4]; obs [n][obs_dim]; rew [n];
+/* env.step(action) under TimeLimit for all envs.  act [n][4] (16-byte aligned); obs [n][obs_dim]
+ * (8-byte aligned; 16-byte aligned rows leave the SM as bulk copies); rew [n];
  * done [n] (1 = terminal or time-limit); cost [n] (info['cost'], may be NULL);
  * term_obs [n][obs_dim] (observation before the auto-reset, written for done envs only; may be NULL);
  * truncated [n] (info['TimeLimit.truncated'], may be NULL). */
@@ -185,6 +186,10 @@ int cf_set_noise_override(cf_env* env, const float* step_normals, const float* s
  * idx [n][6] int32, dstb [n][2] float32 sign codes (+1/-1); HOST pointers. */
 int cf_hj_lookup_host(cf_env* env, int32_t level_idx, const double* states, int32_t n,
                       int32_t* idx, float* dstb_sign);
+/* the same for float32 states [n][6] through the step kernel's own float32 rule (per-boundary float32
+ * thresholds derived on the host from the float64 rule): must equal cf_hj_lookup_host on (double)state */
+int cf_hj_lookup_f32_host(cf_env* env, int32_t level_idx, const float* states, int32_t n,
+                          int32_t* idx, float* dstb_sign);
 
 /* ---- PPO GAE (Buffer.finish_path, algs/core.py:498-535; discount_cumsum :105-119) ----- */
 /* Time-major rollout [T][N].  A path ends after step t of env n when done[t][n] != 0; its
@@ -215,6 +220,14 @@ int64_t cf_launch_count(const cf_env* env);
 /* average device time (ms) of the step kernel launches since the last call with reset!=0,
  * measured with CUDA events on the launching stream when profiling was enabled */
 int cf_kernel_timing(cf_env* env, int32_t enable, int32_t reset, double* avg_ms, int64_t* launches);
+
+/* Tracing hook: when `trace_dev` (DEVICE pointer, [cf_num_tiles][16] uint64, caller-owned, zeroed by the caller)
+ * is set, every step launch records per tile (times in %globaltimer ns): [0] SM id, [1] CTA start, [2] state tile
+ * landed in shared memory, [3..6] warp 0..3 finished the step phase, [7] tile barrier passed, [8] in-place resets
+ * done, [9] CTA end, [10] envs of the tile that finished an episode.  NULL switches tracing off (the default;
+ * no cost beyond a predicate). */
+int cf_set_trace_buffer(cf_env* env, uint64_t* trace_dev);
+int cf_num_tiles(const cf_env* env);     /* tiles of envs the step kernel launches (one CTA each) */
 
 const char* cf_last_error(void);
 int cf_abi_version(void);

@@ -91,7 +91,8 @@ static void philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t
 }
 void cfo_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { philox4x32_10(ctr, key, out); }
 
-static double u01(uint32_t w) { return ((double)(w >> 8) + 0.5) * (1.0 / 16777216.0); }
+/* 23 random bits -> (2k+1)/2^24, the value the CUDA side builds with the mantissa trick */
+static double u01(uint32_t w) { return ((double)(w >> 9) * 2.0 + 1.0) * (1.0 / 16777216.0); }
 
 /* standard draws of one RNG event: normals block b -> z[4b..4b+3]; uniform block b -> counter 16+b */
 static void draw_event(const cfo_env* e, uint32_t ctr1, uint32_t tag, int n_norm, int n_unif,
@@ -219,6 +220,7 @@ void cfo_hj_index(const double s[6], int idx[6]) {
     for (int d = 0; d < 6; ++d) {
         const double* g = g_grid[d];
         int i = 0;
+        if (s[d] != s[d]) i = 15;                               /* np.searchsorted sorts NaN last */
         while (i < 15 && g[i] < s[d]) ++i;                      /* np.searchsorted, side='left' */
         if (i > 0 && (i == 15 || fabs(s[d] - g[i - 1]) < fabs(s[d] - g[i]))) i -= 1;
         idx[d] = i;

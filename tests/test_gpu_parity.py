@@ -140,6 +140,84 @@ def test_hj_indices_and_signs_bit_exact():
         env.close()
 
 
+def test_hj_float32_threshold_rule_bit_exact():
+    """The step kernel indexes float32 states with per-boundary float32 thresholds; that must equal the
+    reference's float64 Grid.get_index on the same (exactly representable) values, ties included."""
+    rng = np.random.default_rng(11)
+    g = co.grid_points()
+    n = 400000
+    states = rng.uniform(-4.0, 4.0, (n, 6)).astype(np.float32)
+    k = rng.integers(0, 15, (6000, 6))
+    pts = np.take_along_axis(g.T, k, axis=0)
+    mids = (0.5 * (pts + np.take_along_axis(g.T, np.minimum(k + 1, 14), axis=0))).astype(np.float32)
+    pts32 = pts.astype(np.float32)
+    blocks = []
+    for base in (pts32, mids):                      # grid points / midpoints and +-1..3 float32 ulps around them
+        x = base.copy()
+        blocks.append(x.copy())
+        up, dn = x.copy(), x.copy()
+        for _ in range(3):
+            up = np.nextafter(up, np.float32(np.inf)); dn = np.nextafter(dn, np.float32(-np.inf))
+            blocks.append(up.copy()); blocks.append(dn.copy())
+    edge = np.concatenate(blocks)
+    states[: len(edge)] = edge
+    states[len(edge)] = [np.inf, -np.inf, 3e38, -3e38, 0.0, -0.0]
+    states[len(edge) + 1] = [np.nan, 0.1, np.nan, -0.1, np.nan, 1e-45]
+    ref_idx = co.hj_index(states.astype(np.float64))
+    V = hj_tables.synthetic_table(1.5, 15)
+    env = CrazyFlieVecEnv('DroneHoverBulletFreeEnvWithAdversary-v0', num_envs=4)
+    idx, sign = env.hj_lookup_f32(1.5, states)
+    assert np.array_equal(idx, ref_idx), 'float32 threshold rule must reproduce the float64 grid indices'
+    bits = co.hj_signbits(V, ref_idx)
+    ref_sign = np.stack([np.where(bits & 1, -1.0, 1.0), np.where(bits & 2, -1.0, 1.0)], axis=1)
+    assert np.array_equal(sign, ref_sign.astype(np.float32))
+    env.close()
+
+
+def test_partial_tile_and_unaligned_rows():
+    """num_envs that is not a multiple of the 128-env tile, and obs buffers the bulk-copy path cannot
+    use (8-byte aligned rows), give the same results as the aligned full-tile path."""
+    import torch
+    n = 300
+    kw = dict(seed=21)
+    a = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=n, **kw)
+    b = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=512, **kw)
+    oa, ob = a.reset().clone(), b.reset().clone()
+    assert torch.equal(oa, ob[:n])
+    act = torch.rand((512, 4), device='cuda') * 0.2
+    # unaligned view for env a: rows start 8 bytes into a 16-byte aligned buffer
+    buf = torch.zeros(n * 34 + 2, device='cuda')
+    L = abi.lib()
+    import ctypes as C
+    p = lambda t: C.c_void_p(t.data_ptr())
+    for _ in range(40):
+        o2, r2, d2, _ = b.step(act)
+        obs_view = buf[2:]
+        abi.check(L.cf_step_dev(a._h, p(act[:n].contiguous()), C.c_void_p(obs_view.data_ptr()), p(a._rew), p(a._done),
+                                p(a._cost), None, None, None))
+        assert torch.equal(obs_view.view(n, 34), o2[:n])
+        assert torch.equal(a._rew, r2[:n])
+        assert torch.equal(a._done.bool(), d2[:n])
+    a.close(); b.close()
+
+
+def test_step_k_matches_single_steps():
+    import torch
+    n, k = 1000, 7
+    kw = dict(seed=33)
+    a = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=n, **kw)
+    b = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=n, **kw)
+    a.reset(); b.reset()
+    acts = (torch.rand((k, n, 4), device='cuda') * 0.4 - 0.1).contiguous()
+    obs_k, rew_k, done_k, cost_k = a.step_k(acts)
+    for t in range(k):
+        o, r, d, info = b.step(acts[t])
+        assert torch.equal(obs_k[t], o) and torch.equal(rew_k[t], r)
+        assert torch.equal(done_k[t].bool(), d) and torch.equal(cost_k[t], info['cost'])
+    assert np.array_equal(a.get_state().view(np.uint32), b.get_state().view(np.uint32))
+    a.close(); b.close()
+
+
 def test_hj_packed_sign_table_matches_oracle():
     import ctypes as C
     env = CrazyFlieVecEnv('DroneHoverBulletFreeEnvWithAdversary-v0', num_envs=4)
