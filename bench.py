@@ -48,6 +48,9 @@ def parse():
     ap.add_argument('--e2e-steps', type=int, default=100)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--streams', type=int, default=1,
+                    help='independent shards are stepped on this many streams (parallel branches of the CUDA graph), so one '
+                         "shard's load/store phases overlap another's compute")
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
@@ -188,6 +191,9 @@ def main_ours(args):
     cost = [torch.empty(n, device=dev) for _ in range(S)]
     P = lambda t: C.c_void_p(t.data_ptr())
 
+    NS = max(1, min(args.streams, S))
+    side_streams = [torch.cuda.Stream(device=dev) for _ in range(NS - 1)]
+
     def step_shard(i):
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         rc = L.cf_step_dev(shards[i]._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, stream)
@@ -198,8 +204,18 @@ def main_ours(args):
         e.reset()
 
     def run(k_steps, offset=0):
+        """k_steps control steps, shard (offset+t) % S on stream t % NS (fork / join around the batch)"""
+        main = torch.cuda.current_stream()
+        for st in side_streams:
+            st.wait_stream(main)
         for t in range(k_steps):
-            step_shard((offset + t) % S)
+            if t % NS == 0:
+                step_shard((offset + t) % S)
+            else:
+                with torch.cuda.stream(side_streams[t % NS - 1]):
+                    step_shard((offset + t) % S)
+        for st in side_streams:
+            main.wait_stream(st)
 
     # ---- warm-up (direct launches), then one CUDA graph of S launches (one control step of every shard) --
     run(W)
@@ -308,7 +324,8 @@ def main_ours(args):
                              'of state + I/O per GPU vs 126 MB L2', 'actions': 'hover + 0.05*N(0,1), resident in HBM',
                        'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
                                     'packed 2-bit sign tables in HBM/L2',
-                       'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S} (one per shard)')},
+                       'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S} (one per shard)')
+                                    + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else '')},
             'clocks': clocks, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
                     'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,

@@ -55,7 +55,7 @@ struct Rng {
     // four standard normals of block b (Box-Muller on two pairs, same pairing as the oracle)
     __device__ __forceinline__ float4 normals(const DevCfg& cfg, uint32_t b) const {
         uint4 w = raw(cfg, b);
-        float r0 = fsqrt(-2.0f * __logf(u01(w.x))), r1 = fsqrt(-2.0f * __logf(u01(w.z)));
+        float r0 = fsqrt(-1.3862943611f * __log2f(u01(w.x))), r1 = fsqrt(-1.3862943611f * __log2f(u01(w.z)));   // sqrt(-2 ln u)
         float s0, c0_, s1, c1_;
         __sincosf(kPi * (2.0f * u01(w.y) - 1.0f), &s0, &c0_);
         __sincosf(kPi * (2.0f * u01(w.w) - 1.0f), &s1, &c1_);
@@ -162,7 +162,7 @@ __device__ __forceinline__ void store_row(float* __restrict__ dst, const float* 
 // btMatrix3x3::setRotation == pybullet.getMatrixFromQuaternion (agents.py:452, physics.py:234)
 __device__ __forceinline__ void quat_to_R(const float q[4], float R[9]) {
     float x = q[0], y = q[1], z = q[2], w = q[3];
-    float d = x * x + y * y + z * z + w * w, s = 2.0f / d;
+    float d = x * x + y * y + z * z + w * w, s = 2.0f * frcp(d);
     float xs = x * s, ys = y * s, zs = z * s;
     float wx = w * xs, wy = w * ys, wz = w * zs, xx = x * xs, xy = x * ys, xz = x * zs;
     float yy = y * ys, yz = y * zs, zz = z * zs;
@@ -193,12 +193,30 @@ __device__ __forceinline__ void quat_to_rpy_bullet(const float q[4], float rpy[3
         rpy[2] = atan2f(2.f * (x * y + w * z), squ + sqx - sqy - sqz);
     }
 }
-// pybullet.getQuaternionFromEuler (hover_free.py:183,255), normalised
+// sin and cos for |x| <= pi/2 (half angles of clipped Euler angles): Taylor polynomials to x^11 / x^12,
+// truncation < 6e-8 relative at the interval end; no range reduction, no slow path.
+__device__ __forceinline__ void sincos_half(float x, float* sn, float* cs) {
+    float x2 = x * x;
+    float ps = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, -2.5052108e-8f, 2.7557319e-6f), -1.9841270e-4f), 8.3333333e-3f),
+                             -1.6666667e-1f), 1.0f);
+    float pc = fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, fmaf(x2, 2.0876757e-9f, -2.7557319e-7f), 2.4801587e-5f), -1.3888889e-3f),
+                                      4.1666667e-2f), -0.5f), 1.0f);
+    *sn = x * ps; *cs = pc;
+}
+// pybullet.getQuaternionFromEuler (hover_free.py:183,255), normalised.  WIDE: any angles (the reset
+// samples yaw in +-2 pi); otherwise |rpy| <= (pi, pi/2, pi) as clipped by compute_observation.
+template <bool WIDE>
 __device__ __forceinline__ void rpy_to_quat(const float rpy[3], float q[4]) {
     float sp, cp, st, ct, ss, cs;
-    sincosf(0.5f * rpy[0], &sp, &cp);
-    sincosf(0.5f * rpy[1], &st, &ct);
-    sincosf(0.5f * rpy[2], &ss, &cs);
+    if (WIDE) {
+        sincosf(0.5f * rpy[0], &sp, &cp);
+        sincosf(0.5f * rpy[1], &st, &ct);
+        sincosf(0.5f * rpy[2], &ss, &cs);
+    } else {
+        sincos_half(0.5f * rpy[0], &sp, &cp);
+        sincos_half(0.5f * rpy[1], &st, &ct);
+        sincos_half(0.5f * rpy[2], &ss, &cs);
+    }
     q[0] = sp * ct * cs - cp * st * ss;
     q[1] = cp * st * cs + sp * ct * ss;
     q[2] = cp * ct * ss - sp * st * cs;
@@ -287,12 +305,10 @@ __device__ __forceinline__ int hj_signbits(const DevTables& tab, int level_idx, 
 // distur_gener (distur_gener.py:19-183) reduced to the two torque components the physics uses:
 // returns the sign bits of the level's table at the nearest grid cell of (rpy, body rates)
 template <int HJ_MODE>
-__device__ __forceinline__ int hj_disturbance_bits(const float q[4], const float ow[3], const DevCfg& cfg,
+__device__ __forceinline__ int hj_disturbance_bits(const float q[4], const float wb[3], const DevCfg& cfg,
                                                    const DevTables& tab, const float* thr, int level_idx) {
-    float rpy[3], R[9], wb[3];
+    float rpy[3];
     quat2euler_hj(q, rpy);
-    quat_to_R(q, R);
-    matTvec(R, ow, wb);
     int idx[6];
 #pragma unroll
     for (int k = 0; k < 3; ++k) { idx[k] = hj_index_f32(rpy[k], k, thr, cfg); idx[3 + k] = hj_index_f32(wb[k], 3 + k, thr, cfg); }
@@ -332,7 +348,7 @@ __device__ __forceinline__ void observe_full(const float pos[3], const float vel
         float th = cfg.quat_std * z[15 + i] + (-cfg.quat_unif + (2.0f * cfg.quat_unif) * u[3 + i]);
         rot[i] = fminf(hi[i], fmaxf(lo[i], rpy[i] + th));
     }
-    rpy_to_quat(rot, obs + 3);
+    rpy_to_quat<false>(rot, obs + 3);
 #pragma unroll
     for (int i = 0; i < 3; ++i) obs[10 + i] = lpf[i];
 }
@@ -348,9 +364,10 @@ struct Body {
 // semi-implicit Euler, exponential-map quaternion update, gyroscopic term, 0.04 damping).
 // `delayed` is the action leaving the latency ring in this substep (agents.py:268-276);
 // invJ / invm are reciprocals of the (domain-randomised) inertia and mass.
-__device__ __forceinline__ void physics_substep(Body& b, const DrParams& p, const float invJ[3], float invm,
-                                                const DevCfg& cfg, const float delayed[4], float d0, float d1,
-                                                const float zou[4]) {
+// R, wb: rotation matrix and body rates of the state before the substep (frame_of).
+__device__ __forceinline__ void physics_substep(Body& b, const float R[9], const float wb[3], const DrParams& p,
+                                                const float invJ[3], float invm, const DevCfg& cfg, const float delayed[4],
+                                                float d0, float d1, const float zou[4]) {
     const float kFtf0 = 1.56e-5f, kArm = 0.028f, kPropZ = 0.0108f, kG = 9.81f;
     const float kDrag[3] = {9.1785e-7f, 9.1785e-7f, 10.311e-7f};
     float f[4], t[4];
@@ -370,9 +387,7 @@ __device__ __forceinline__ void physics_substep(Body& b, const DrParams& p, cons
     }
     rpm_sum *= 2.0f * kPi * 25000.0f / 60.0f;                 // sum_i 2 pi (25000 x_i^2) / 60, physics.py:236
     float zt = ((-t[0] + t[1]) - t[2]) + t[3];
-    float R[9], wb[3], vb[3];
-    quat_to_R(b.quat, R);
-    matTvec(R, b.ow, wb);
+    float vb[3];
     matTvec(R, b.vel, vb);
     // drag (physics.py:232-241): R @ (k * v_world) handed to Bullet as a LINK_FRAME force
     float kv[3], drag_link[3];
@@ -527,7 +542,7 @@ __device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const 
             e.f(CF_S_RING + i, r);
             if (i >= 4) la[i - 4] = r;                      // view of action_buffer[-1,:], agents.py:386
         }
-        rpy_to_quat(rpy, quat);
+        rpy_to_quat<true>(rpy, quat);
     } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) e.f(CF_S_RING + i, 0.0f);
@@ -630,7 +645,9 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     int bits = 0;
     const int level = misc_level(misc);
     const bool hj = (cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0;
-    if (hj) bits = hj_disturbance_bits<HJ_MODE>(b.quat, b.ow, cfg, tab, thr, level);
+    float R[9], wb[3];
+    quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame of the pre-step state: HJ lookup and substep 1
+    if (hj) bits = hj_disturbance_bits<HJ_MODE>(b.quat, wb, cfg, tab, thr, level);
     float d0 = 0.0f, d1 = 0.0f;
     if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {                // dstb_space.sample(), hover_free.py:868-878
         float4 ub = dw.u(cfg, 1);
@@ -657,14 +674,13 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     // gyro sample survives (bias walk + low-pass), the rest of that call is overwritten below
     {
         const float zou[4] = {zq.x, zq.y, zq.z, zq.w};
-        physics_substep(b, p, invJ, invm, cfg, del1, d0, d1, zou);
+        physics_substep(b, R, wb, p, invJ, invm, cfg, del1, d0, d1, zou);
     }
-    float R[9], wb[3];
+    quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame after substep 1: gyro sample and substep 2
     float4 z3;
     if (NOISE) {
         float4 z1 = dw.z(cfg, 1), z2 = dw.z(cfg, 2);
         z3 = dw.z(cfg, 3);
-        quat_to_R(b.quat, R); matTvec(R, b.ow, wb);
         const float zb[3] = {z1.x, z1.y, z1.z}, zr[3] = {z1.w, z2.x, z2.y}, zt[3] = {z2.z, z2.w, z3.x};
         gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
     } else {
@@ -673,7 +689,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     float4 z4 = dw.z(cfg, 4);
     {
         const float zou[4] = {z3.y, z3.z, z3.w, z4.x};
-        physics_substep(b, p, invJ, invm, cfg, del2, d0, d1, zou);
+        physics_substep(b, R, wb, p, invJ, invm, cfg, del2, d0, d1, zou);
     }
     // final rigid-body state back to the tile; true attitude and body rates (agents.py:434-453)
     e.set3(CF_S_POS, b.pos); e.set4(CF_S_QUAT, b.quat); e.set3(CF_S_VEL, b.vel); e.set3(CF_S_OMEGA_W, b.ow);
@@ -731,7 +747,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     bool dn = b.pos[2] < 0.2f;
     dn |= fabsf(rpy[0]) > cfg.done_rp_rad || fabsf(rpy[1]) > cfg.done_rp_rad;
 #pragma unroll
-    for (int i = 0; i < 3; ++i) dn |= (180.0f * fabsf(wb[i]) / kPi) > cfg.done_rate_deg;
+    for (int i = 0; i < 3; ++i) dn |= (fabsf(wb[i]) * (180.0f / kPi)) > cfg.done_rate_deg;
     float nca = 0.0f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) { float c = 0.5f * (clampf(a[i], -1.0f, 1.0f) + 1.0f); nca += c * c; }

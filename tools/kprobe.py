@@ -26,6 +26,7 @@ def main():
     ap.add_argument('--shards', type=int, default=8)
     ap.add_argument('--steps', type=int, default=400)
     ap.add_argument('--traces', type=int, default=3)
+    ap.add_argument('--streams', type=int, nargs='*', default=[1])
     ap.add_argument('--kw', nargs='*', default=[])
     a = ap.parse_args()
     kw = {}
@@ -57,19 +58,30 @@ def main():
     for t in range(200):
         step(t % S)
     torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        for i in range(S):
-            step(i)
-    graph.replay(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = max(1, a.steps // S)
-    e0.record()
-    for _ in range(reps):
-        graph.replay()
-    e1.record(); torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) * 1e3 / (reps * S)
-    print(f'[{a.env_id} {kw}] graph replay: {us:.2f} us/step  {n / us * 1e6:.3e} env-steps/s')
+    for ns in a.streams:
+        side = [torch.cuda.Stream(device=dev) for _ in range(ns - 1)]
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            main = torch.cuda.current_stream()
+            for st in side:
+                st.wait_stream(main)
+            for i in range(S):
+                if i % ns == 0:
+                    step(i)
+                else:
+                    with torch.cuda.stream(side[i % ns - 1]):
+                        step(i)
+            for st in side:
+                main.wait_stream(st)
+        graph.replay(); torch.cuda.synchronize()
+        reps = max(1, a.steps // S)
+        e0.record()
+        for _ in range(reps):
+            graph.replay()
+        e1.record(); torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (reps * S)
+        print(f'[{a.env_id} {kw}] graph replay, {ns} stream(s): {us:.2f} us/step  {n / us * 1e6:.3e} env-steps/s')
     # direct launches, one at a time with a sync in between (isolated kernel time)
     ts = []
     for t in range(16):
