@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'csrc', 'libcf_b200.so')
+LIB_PATH = os.environ.get('CF_LIB_PATH') or os.path.join(HERE, 'csrc', 'libcf_b200.so')   # override: experimental builds (tools/)
 
 CF_ABI_VERSION = 1
 CF_OK, CF_ERR_INVALID, CF_ERR_CUDA, CF_ERR_NO_TABLE, CF_ERR_ALLOC = 0, -1, -2, -3, -4

@@ -29,17 +29,19 @@ def is_stale() -> bool:
     return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
+def build(force: bool = False, verbose: bool = False, extra_flags=(), out: str = OUT) -> str:
+    """``extra_flags`` / ``out`` build an experimental variant (e.g. ``-DCF_TILE=64``) next to the product library;
+    ``CF_LIB_PATH`` makes :mod:`abi` load it (tools/ only)."""
+    if not force and not extra_flags and out == OUT and not is_stale():
         return OUT
-    cmd = [nvcc_path()] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ['-o', OUT]
+    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra_flags) + (['-Xptxas', '-v'] if verbose else []) + \
+          [os.path.join(CSRC, s) for s in SOURCES] + ['-o', out]
     p = subprocess.run(cmd, capture_output=True, text=True)
     if p.returncode != 0:
         raise RuntimeError('nvcc failed:\n' + ' '.join(cmd) + '\n' + p.stdout + p.stderr)
     if verbose:
         print(p.stderr)
-    return OUT
+    return out
 
 
 if __name__ == '__main__':

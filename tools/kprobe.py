@@ -27,6 +27,7 @@ def main():
     ap.add_argument('--steps', type=int, default=400)
     ap.add_argument('--traces', type=int, default=3)
     ap.add_argument('--streams', type=int, nargs='*', default=[1])
+    ap.add_argument('--graph-reps', type=int, nargs='*', default=[1], help='round-robin passes over the shards captured per graph')
     ap.add_argument('--kw', nargs='*', default=[])
     a = ap.parse_args()
     kw = {}
@@ -60,28 +61,30 @@ def main():
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for ns in a.streams:
+      for gr in a.graph_reps:
         side = [torch.cuda.Stream(device=dev) for _ in range(ns - 1)]
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             main = torch.cuda.current_stream()
             for st in side:
                 st.wait_stream(main)
-            for i in range(S):
-                if i % ns == 0:
+            for j in range(S * gr):
+                i = j % S
+                if j % ns == 0:
                     step(i)
                 else:
-                    with torch.cuda.stream(side[i % ns - 1]):
+                    with torch.cuda.stream(side[j % ns - 1]):
                         step(i)
             for st in side:
                 main.wait_stream(st)
         graph.replay(); torch.cuda.synchronize()
-        reps = max(1, a.steps // S)
+        reps = max(1, a.steps // (S * gr))
         e0.record()
         for _ in range(reps):
             graph.replay()
         e1.record(); torch.cuda.synchronize()
-        us = e0.elapsed_time(e1) * 1e3 / (reps * S)
-        print(f'[{a.env_id} {kw}] graph replay, {ns} stream(s): {us:.2f} us/step  {n / us * 1e6:.3e} env-steps/s')
+        us = e0.elapsed_time(e1) * 1e3 / (reps * S * gr)
+        print(f'[{a.env_id} {kw}] graph of {S * gr} launches, {ns} stream(s): {us:.2f} us/step  {n / us * 1e6:.3e} env-steps/s', flush=True)
     # direct launches, one at a time with a sync in between (isolated kernel time)
     ts = []
     for t in range(16):
