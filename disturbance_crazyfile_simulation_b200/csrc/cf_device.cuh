@@ -302,18 +302,31 @@ __device__ __forceinline__ int hj_signbits(const DevTables& tab, int level_idx, 
     if (HJ_MODE == CF_HJ_SIGN_TABLE) return hj_signbits_packed(tab.signs + (size_t)level_idx * CF_SIGN_STRIDE, idx);
     return hj_signbits_value(tab.value[level_idx], idx);
 }
-// distur_gener (distur_gener.py:19-183) reduced to the two torque components the physics uses:
-// returns the sign bits of the level's table at the nearest grid cell of (rpy, body rates)
+// distur_gener (distur_gener.py:19-183) reduced to the two torque components the physics uses: the sign bits
+// of the level's table at the nearest grid cell of (rpy, body rates).  Split in two so that the gather is in
+// flight while the motor model runs: `issue` returns the raw table byte (packed mode) or the decoded bits
+// (value-table mode) plus the shift, `hj_bits` extracts the two bits where the torque is needed.
+struct HjFetch { uint32_t raw; int shift; };
 template <int HJ_MODE>
-__device__ __forceinline__ int hj_disturbance_bits(const float q[4], const float wb[3], const DevCfg& cfg,
-                                                   const DevTables& tab, const float* thr, int level_idx) {
+__device__ __forceinline__ HjFetch hj_disturbance_issue(const float q[4], const float wb[3], const DevCfg& cfg,
+                                                        const DevTables& tab, const float* thr, int level_idx) {
     float rpy[3];
     quat2euler_hj(q, rpy);
     int idx[6];
 #pragma unroll
     for (int k = 0; k < 3; ++k) { idx[k] = hj_index_f32(rpy[k], k, thr, cfg); idx[3 + k] = hj_index_f32(wb[k], 3 + k, thr, cfg); }
-    return hj_signbits<HJ_MODE>(tab, level_idx, idx);
+    HjFetch f;
+    if (HJ_MODE == CF_HJ_SIGN_TABLE) {
+        const int c = hj_cell(idx);
+        f.raw = __ldg(tab.signs + (size_t)level_idx * CF_SIGN_STRIDE + (c >> 2));
+        f.shift = 2 * (c & 3);
+    } else {
+        f.raw = (uint32_t)hj_signbits_value(tab.value[level_idx], idx);
+        f.shift = 0;
+    }
+    return f;
 }
+__device__ __forceinline__ int hj_bits(const HjFetch& f) { return (int)((f.raw >> f.shift) & 3u); }
 
 // ---------------------------------------------------------------------------------- sensors
 // SensorNoise.add_noise_to_omega (envs/sensors.py:121-134) at dt = 1/SIM_FREQ, followed by
@@ -331,16 +344,15 @@ __device__ __forceinline__ void gyro_update(float bias[3], float lpf[3], const D
 // The 100 Hz branch of compute_observation (hover_free.py:168-200) with SensorNoise.add_noise
 // (sensors.py:75-119).  Normal blocks zb0.. cover 18 slots starting at slot offset `off` inside
 // block zb0: pos3, vel3, gyro9 (bias, random walk, turn-on), rot3; uniforms: pos3, rot3.
-__device__ __forceinline__ void observe_full(const float pos[3], const float vel[3], const float rpy[3], const float wb[3],
-                                             float bias[3], float lpf[3], const DevCfg& cfg, const float z[18],
-                                             const float u[6], float obs[13]) {
+// the part of it that does not involve the gyro: noisy position, velocity and attitude quaternion -> obs[0:10]
+__device__ __forceinline__ void observe_nongyro(const float pos[3], const float vel[3], const float rpy[3], const DevCfg& cfg,
+                                                const float z[18], const float u[6], float obs[13]) {
     const float kPosStd = 0.002f, kPosUnif = 0.001f, kVelStd = 0.01f;     // sensors.py:18-25
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         obs[i] = pos[i] + (kPosStd * z[i] + (-kPosUnif + (2.0f * kPosUnif) * u[i]));
         obs[7 + i] = vel[i] + kVelStd * z[3 + i];                          // vel_unif_range = 0
     }
-    gyro_update(bias, lpf, cfg, wb, z + 6, z + 9, z + 12);
     const float lo[3] = {-kPi, -0.5f * kPi, -kPi}, hi[3] = {kPi, 0.5f * kPi, kPi};
     float rot[3];
 #pragma unroll
@@ -349,6 +361,12 @@ __device__ __forceinline__ void observe_full(const float pos[3], const float vel
         rot[i] = fminf(hi[i], fmaxf(lo[i], rpy[i] + th));
     }
     rpy_to_quat<false>(rot, obs + 3);
+}
+__device__ __forceinline__ void observe_full(const float pos[3], const float vel[3], const float rpy[3], const float wb[3],
+                                             float bias[3], float lpf[3], const DevCfg& cfg, const float z[18],
+                                             const float u[6], float obs[13]) {
+    observe_nongyro(pos, vel, rpy, cfg, z, u, obs);
+    gyro_update(bias, lpf, cfg, wb, z + 6, z + 9, z + 12);
 #pragma unroll
     for (int i = 0; i < 3; ++i) obs[10 + i] = lpf[i];
 }
@@ -365,9 +383,12 @@ struct Body {
 // `delayed` is the action leaving the latency ring in this substep (agents.py:268-276);
 // invJ / invm are reciprocals of the (domain-randomised) inertia and mass.
 // R, wb: rotation matrix and body rates of the state before the substep (frame_of).
+// d0, d1: adversary roll / pitch torque; with DECODE they are extracted here from the table fetch issued at
+// the top of the step (distur_gener.py:106-125: -dmax where dV/dx > 0, else +dmax), as late as the data flow allows.
+template <bool DECODE>
 __device__ __forceinline__ void physics_substep(Body& b, const float R[9], const float wb[3], const DrParams& p,
                                                 const float invJ[3], float invm, const DevCfg& cfg, const float delayed[4],
-                                                float d0, float d1, const float zou[4]) {
+                                                float& d0, float& d1, const float zou[4], const HjFetch& hjf, bool hj, float dmax) {
     const float kFtf0 = 1.56e-5f, kArm = 0.028f, kPropZ = 0.0108f, kG = 9.81f;
     const float kDrag[3] = {9.1785e-7f, 9.1785e-7f, 10.311e-7f};
     float f[4], t[4];
@@ -412,8 +433,7 @@ __device__ __forceinline__ void physics_substep(Body& b, const float R[9], const
     }
     // body-frame wrench: thrust at the prop positions (agents.py:311-321, urdf:59,85,111,136),
     // yaw torque (:330-337), adversary roll/pitch torques (:517-533)
-    float tau[3] = {kArm * (-fe[0] - fe[1] + fe[2] + fe[3]) + d0,
-                    kArm * (-fe[0] + fe[1] + fe[2] - fe[3]) + d1, zt};
+    float tau[3] = {kArm * (-fe[0] - fe[1] + fe[2] + fe[3]), kArm * (-fe[0] + fe[1] + fe[2] - fe[3]), zt};
     float fb[3] = {drag_link[0], drag_link[1], drag_link[2] + (fe[0] + fe[1] + fe[2] + fe[3])};
     float gz = -kG * p.mass;
     float gb[3] = {R[6] * gz, R[7] * gz, R[8] * gz};        // R^T (0,0,-g m)
@@ -427,6 +447,12 @@ __device__ __forceinline__ void physics_substep(Body& b, const float R[9], const
     float vn = fsqrt(vb[0] * vb[0] + vb[1] * vb[1] + vb[2] * vb[2]);
     float ka = cfg.ang_damp, kl = cfg.lin_damp;
     float alpha_b[3], acc_b[3], alpha_w[3], acc_w[3];
+    if (DECODE && hj) {
+        const int bits = hj_bits(hjf);
+        d0 = (bits & 1) ? -dmax : dmax;
+        d1 = (bits & 2) ? -dmax : dmax;
+    }
+    tau[0] += d0; tau[1] += d1;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         alpha_b[i] = (tau[i] - Jw[i] * (ka + ka * wn)) * invJ[i];
@@ -492,67 +518,80 @@ __device__ __forceinline__ void consume_fresh(const EnvRef e, const DevCfg& cfg,
     e.u(CF_S_MISC, m & 0x7fffffffu);
 }
 
-// All standard draws of a reset event, slot order of the oracle: z[48], u[44] (42 used).
-__device__ __forceinline__ void reset_draws(const DrawSrc& dw, const DevCfg& cfg, float* z, float* u) {
-#pragma unroll
-    for (int b = 0; b < CF_RESET_NORMALS / 4; ++b) { float4 v = dw.z(cfg, b); z[4 * b] = v.x; z[4 * b + 1] = v.y; z[4 * b + 2] = v.z; z[4 * b + 3] = v.w; }
-#pragma unroll
-    for (int b = 0; b < (CF_RESET_UNIFORMS + 3) / 4; ++b) { float4 v = dw.u(cfg, b); u[4 * b] = v.x; u[4 * b + 1] = v.y; u[4 * b + 2] = v.z; u[4 * b + 3] = v.w; }
-}
-
 // reset(): envs/base.py:420-464, task_specific_reset hover_free.py:237-289 / hover.py:1463-1513,
 // apply_domain_randomization base.py:241-298 (+ agents.py:208-224), RandomHJ level draw
 // hover_free.py:536.  Draw slots: z[0:4] motor x, z[4:12] latency ring, z[12:30] and z[30:48]
 // the two compute_observation calls; u[0:14] initial state, u[14:29] DR, u[29:35], u[35:41]
-// observation uniforms, u[41] Boltzmann.  `e` holds the dynamic words (shared or global), `g` the
-// env in global memory (the domain-randomised words are written there); nz / un: the event's
-// standard draws (shared-memory scratch filled by the warp, or thread-local); row: obs_dim floats.
-template <bool NOISE>
-__device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const DevCfg& cfg, const float* nz, const float* un,
-                                          float* row) {
-    constexpr int OD = NOISE ? 34 : 42;
-    // stale body rate of the previous state, read before anything moves (base.py:444 before :448)
-    float stale_wb[3];
-    {
-        float q[4], ow[3], R[9];
-        e.get4(CF_S_QUAT, q); e.get3(CF_S_OMEGA_W, ow);
-        quat_to_R(q, R);
-        matTvec(R, ow, stale_wb);
-    }
-    int level = misc_level(e.u(CF_S_MISC));
-    e.u(CF_S_EP_LEN, 0u); e.f(CF_S_EP_RET, 0.0f);
-    // drone.reset(), agents.py:377-386, then task_specific_reset
-    float pos[3] = {0.f, 0.f, 1.f}, rpy[3] = {0.f, 0.f, 0.f}, vel[3] = {0.f, 0.f, 0.f}, rate[3] = {0.f, 0.f, 0.f};
-    float quat[4] = {0.f, 0.f, 0.f, 1.f}, x[4] = {0.f, 0.f, 0.f, 0.f}, la[4] = {0.f, 0.f, 0.f, 0.f};
+// observation uniforms, u[41] Boltzmann.
+// The reset is written as independent tasks so that the step kernel can run them on different warps
+// (one finished env per lane); reset_env below composes the same tasks serially for the reset kernel.
+
+// What the gyro task needs from the previous episode and from the pose task.
+struct ResetCtx {
+    float stale_wb[3], bias0[3];      // previous state's body rate (base.py:444 runs before :448), gyro bias (never reset)
+    float wb[3];
+};
+// the sampled kinematic state of task_specific_reset (hover_free.py:249-274), a function of the uniforms only
+struct ResetKin { float pos[3], rpy[3], vel[3], rate[3], rpy_t[3]; };
+__device__ __forceinline__ void reset_sample_kin(const DevCfg& cfg, const float* un, ResetKin& k) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { k.pos[i] = 0.f; k.rpy[i] = 0.f; k.vel[i] = 0.f; k.rate[i] = 0.f; }
+    k.pos[2] = 1.f;
     if (cfg.reset_dist) {
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            pos[i] += unif(-cfg.init_pos, cfg.init_pos, un[i]);
-            rpy[i] = unif(-cfg.init_angle, cfg.init_angle, un[3 + i]);
-            vel[i] = unif(-cfg.init_vel, cfg.init_vel, un[7 + i]);
-            rate[i] = unif(-cfg.init_rate, cfg.init_rate, un[10 + i]);
+            k.pos[i] += unif(-cfg.init_pos, cfg.init_pos, un[i]);
+            k.rpy[i] = unif(-cfg.init_angle, cfg.init_angle, un[3 + i]);
+            k.vel[i] = unif(-cfg.init_vel, cfg.init_vel, un[7 + i]);
+            k.rate[i] = unif(-cfg.init_rate, cfg.init_rate, un[10 + i]);
         }
-        rpy[2] = unif(-cfg.init_yaw, cfg.init_yaw, un[6]);
-        rate[2] = unif(-cfg.init_yaw_rate, cfg.init_yaw_rate, un[13]);
+        k.rpy[2] = unif(-cfg.init_yaw, cfg.init_yaw, un[6]);
+        k.rate[2] = unif(-cfg.init_yaw_rate, cfg.init_yaw_rate, un[13]);
+    }
+    // getEulerFromQuaternion(getQuaternionFromEuler(rpy)) (agents.py:446): |roll|, |pitch| <= init_angle < pi/2, so it
+    // returns the sampled roll and pitch and the yaw wrapped into [-pi, pi]
+    k.rpy_t[0] = k.rpy[0]; k.rpy_t[1] = k.rpy[1];
+    k.rpy_t[2] = k.rpy[2] > kPi ? k.rpy[2] - 2.0f * kPi : (k.rpy[2] < -kPi ? k.rpy[2] + 2.0f * kPi : k.rpy[2]);
+}
+// last_action after reset = action_buffer[-1,:] (agents.py:386), a function of the normals only
+__device__ __forceinline__ void reset_sample_la(const DevCfg& cfg, const float* nz, float la[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) la[i] = cfg.reset_dist ? clampf(cfg.hover_a + 0.02f * nz[8 + i], -1.0f, 1.0f) : 0.0f;
+}
+// task 0 (reads the OLD state): stale rpy_dot and the gyro bias carried over (sensors.py:68)
+__device__ __forceinline__ void reset_task_stale(const EnvRef e, ResetCtx& c) {
+    float q[4], ow[3], R[9];
+    e.get4(CF_S_QUAT, q); e.get3(CF_S_OMEGA_W, ow);
+    quat_to_R(q, R);
+    matTvec(R, ow, c.stale_wb);
+    e.get3(CF_S_GYRO_BIAS, c.bias0);
+}
+// task 1: drone.reset() (agents.py:377-386) + task_specific_reset: pose, velocities, motor state, latency ring
+__device__ __forceinline__ void reset_task_pose(const EnvRef e, const DevCfg& cfg, const float* nz, const float* un, float wb[3]) {
+    ResetKin k;
+    reset_sample_kin(cfg, un, k);
+    float quat[4] = {0.f, 0.f, 0.f, 1.f}, x[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cfg.reset_dist) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) x[i] = cfg.hover_x + 0.02f * nz[i];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float r = clampf(cfg.hover_a + 0.02f * nz[4 + i], -1.0f, 1.0f);
-            e.f(CF_S_RING + i, r);
-            if (i >= 4) la[i - 4] = r;                      // view of action_buffer[-1,:], agents.py:386
-        }
-        rpy_to_quat<true>(rpy, quat);
+        for (int i = 0; i < 8; ++i) e.f(CF_S_RING + i, clampf(cfg.hover_a + 0.02f * nz[4 + i], -1.0f, 1.0f));
+        rpy_to_quat<true>(k.rpy, quat);
     } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) e.f(CF_S_RING + i, 0.0f);
     }
-    e.set3(CF_S_POS, pos); e.set4(CF_S_QUAT, quat); e.set3(CF_S_VEL, vel); e.set4(CF_S_MOTOR_X, x);
-    float R[9], ow[3], wb[3];
+    e.set3(CF_S_POS, k.pos); e.set4(CF_S_QUAT, quat); e.set3(CF_S_VEL, k.vel); e.set4(CF_S_MOTOR_X, x);
+    float R[9], ow[3];
     quat_to_R(quat, R);
-    matTvec(R, rate, ow);                                   // resetBaseVelocity(angularVelocity = R.T @ rpy_dot), hover_free.py:283-289
+    matTvec(R, k.rate, ow);                                 // resetBaseVelocity(angularVelocity = R.T @ rpy_dot), hover_free.py:283-289
     e.set3(CF_S_OMEGA_W, ow);
     matTvec(R, ow, wb);                                     // update_information: R.T again (agents.py:452-453)
+}
+// task 2: apply_domain_randomization (written to the env's words in HBM), episode counters, level draw
+__device__ __forceinline__ void reset_task_params(const EnvRef e, const EnvRef g, const DevCfg& cfg, const float* un) {
+    int level = misc_level(e.u(CF_S_MISC));
+    e.u(CF_S_EP_LEN, 0u); e.f(CF_S_EP_RET, 0.0f);
     if (cfg.dr_on) {
         // un[14..28]: dt, mass, Jxx, Jyy, Jzz, (ftf0: cancels in the yaw torque), ftf1, motor tc[4], t2w[4]
         float f = cfg.dr;
@@ -573,41 +612,6 @@ __device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const 
         }
         p.store(g);
     }
-    // gyro_lpf.set(stale rpy_dot), base.py:444; two compute_observation() calls: base.py:453 and, via
-    // compute_history, :308
-    float hist[OD];
-    float ob[13];
-    if (NOISE) {
-        float bias[3], lpf[3] = {stale_wb[0], stale_wb[1], stale_wb[2]}, rpy_t[3];
-        e.get3(CF_S_GYRO_BIAS, bias);
-        quat_to_rpy_bullet(quat, rpy_t);
-        observe_full(pos, vel, rpy_t, wb, bias, lpf, cfg, nz + 12, un + 29, ob);
-#pragma unroll
-        for (int i = 0; i < 13; ++i) hist[i] = ob[i];
-        observe_full(pos, vel, rpy_t, wb, bias, lpf, cfg, nz + 30, un + 35, ob);
-        e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
-#pragma unroll
-        for (int i = 0; i < 13; ++i) hist[17 + i] = ob[i];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { hist[13 + i] = la[i]; hist[30 + i] = la[i]; }
-    } else {
-        e.set3(CF_S_LPF, stale_wb);
-#pragma unroll
-        for (int i = 0; i < 3; ++i) { ob[i] = pos[i]; ob[7 + i] = vel[i]; ob[10 + i] = wb[i]; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) ob[3 + i] = quat[i];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-#pragma unroll
-            for (int i = 0; i < 13; ++i) hist[21 * h + i] = ob[i];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) { hist[21 * h + 13 + i] = la[i]; hist[21 * h + 17 + i] = la[i]; }
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 13; ++i) e.f(CF_S_OBS_PREV + i, ob[i]);
-    e.set4(CF_S_ACT_PREV1, la); e.set4(CF_S_ACT_PREV2, la);
-    store_row<OD>(row, hist);
     // Boltzmann() at the end of reset, hover_free.py:536: cdf.searchsorted(u, side='right') =
     // #{k : cdf[k] <= u}; for a float32 u that is #{k : u >= boltz_thr[k]} with boltz_thr[k] the smallest
     // float32 >= cdf[k] (derived on the host)
@@ -620,8 +624,137 @@ __device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const 
     }
     e.u(CF_S_MISC, misc_pack(level, 0, 0, false));
 }
+// tasks 3 / 4 (noise on): the gyro-free part of the two compute_observation calls of reset (base.py:453 and,
+// via compute_history, :308): WHICH = 0 -> obs(k-1) = row[0:10], WHICH = 1 -> obs(k) = row[17:27] and the
+// env's last-emitted observation; task 4 also writes the action history (base.py:459-460)
+template <int WHICH>
+__device__ __forceinline__ void reset_task_obs_nongyro(const EnvRef e, const DevCfg& cfg, const float* nz, const float* un, float* row) {
+    ResetKin k;
+    reset_sample_kin(cfg, un, k);
+    float ob[13];
+    observe_nongyro(k.pos, k.vel, k.rpy_t, cfg, nz + 12 + 18 * WHICH, un + 29 + 6 * WHICH, ob);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) row[17 * WHICH + i] = ob[i];
+    if (WHICH == 1) {
+#pragma unroll
+        for (int i = 0; i < 10; ++i) e.f(CF_S_OBS_PREV + i, ob[i]);
+        float la[4];
+        reset_sample_la(cfg, nz, la);
+        e.set4(CF_S_ACT_PREV1, la); e.set4(CF_S_ACT_PREV2, la);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { row[13 + i] = la[i]; row[30 + i] = la[i]; }
+    }
+}
+// task 5 (noise on): gyro_lpf.set(stale rpy_dot), base.py:444, then the gyro samples of the two observations
+__device__ __forceinline__ void reset_task_gyro(const EnvRef e, const ResetCtx& c, const DevCfg& cfg, const float* nz, float* row) {
+    float bias[3], lpf[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { bias[i] = c.bias0[i]; lpf[i] = c.stale_wb[i]; }
+    gyro_update(bias, lpf, cfg, c.wb, nz + 12 + 6, nz + 12 + 9, nz + 12 + 12);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) row[10 + i] = lpf[i];
+    gyro_update(bias, lpf, cfg, c.wb, nz + 30 + 6, nz + 30 + 9, nz + 30 + 12);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { row[27 + i] = lpf[i]; e.f(CF_S_OBS_PREV + 10 + i, lpf[i]); }
+    e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
+}
 
-// ---------------------------------------------------------------------------------- step
+// All standard draws of a reset event, slot order of the oracle: z[48], u[44] (42 used).
+__device__ __forceinline__ void reset_draws(const DrawSrc& dw, const DevCfg& cfg, float* z, float* u) {
+#pragma unroll
+    for (int b = 0; b < CF_RESET_NORMALS / 4; ++b) { float4 v = dw.z(cfg, b); z[4 * b] = v.x; z[4 * b + 1] = v.y; z[4 * b + 2] = v.z; z[4 * b + 3] = v.w; }
+#pragma unroll
+    for (int b = 0; b < (CF_RESET_UNIFORMS + 3) / 4; ++b) { float4 v = dw.u(cfg, b); u[4 * b] = v.x; u[4 * b + 1] = v.y; u[4 * b + 2] = v.z; u[4 * b + 3] = v.w; }
+}
+
+// The whole reset of one env by one thread (reset kernel; in-place resets of the noise-free variant).
+// `e` holds the dynamic words (shared or global), `g` the env in global memory (the domain-randomised
+// words are written there); nz / un: the event's standard draws; row: obs_dim floats.
+template <bool NOISE>
+__device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const DevCfg& cfg, const float* nz, const float* un,
+                                          float* row) {
+    constexpr int OD = NOISE ? 34 : 42;
+    ResetCtx c;
+    reset_task_stale(e, c);
+    reset_task_pose(e, cfg, nz, un, c.wb);
+    reset_task_params(e, g, cfg, un);
+    if (NOISE) {
+        reset_task_obs_nongyro<0>(e, cfg, nz, un, row);
+        reset_task_obs_nongyro<1>(e, cfg, nz, un, row);
+        reset_task_gyro(e, c, cfg, nz, row);
+    } else {
+        ResetKin k;
+        reset_sample_kin(cfg, un, k);
+        float la[4], quat[4], hist[OD], ob[13];
+        reset_sample_la(cfg, nz, la);
+        e.set3(CF_S_LPF, c.stale_wb);
+        e.get4(CF_S_QUAT, quat);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { ob[i] = k.pos[i]; ob[7 + i] = k.vel[i]; ob[10 + i] = c.wb[i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ob[3 + i] = quat[i];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int i = 0; i < 13; ++i) hist[21 * h + i] = ob[i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { hist[21 * h + 13 + i] = la[i]; hist[21 * h + 17 + i] = la[i]; }
+        }
+#pragma unroll
+        for (int i = 0; i < 13; ++i) e.f(CF_S_OBS_PREV + i, ob[i]);
+        e.set4(CF_S_ACT_PREV1, la); e.set4(CF_S_ACT_PREV2, la);
+        store_row<OD>(row, hist);
+    }
+}
+
+// Standard draws of a step event, produced BEFORE the state tile has landed (they depend on the env id and
+// the event counter only): normal blocks 0..3 in registers, blocks 4..10 and the six observation uniforms in
+// `s` - 34 words of warp-local shared-memory scratch, word-major ([slot][lane], conflict-free), which is the
+// warp's own 32 observation rows: they are written only after the last draw has been read.
+struct StepDraws {
+    float4 r0, r1, r2, r3;
+    float ubox0, ubox1;
+    const float* s;
+    template <int B>
+    __device__ __forceinline__ float4 z() const {
+        if (B == 0) return r0;
+        if (B == 1) return r1;
+        if (B == 2) return r2;
+        if (B == 3) return r3;
+        const float* p = s + (4 * (B - 4)) * 32;
+        return make_float4(p[0], p[32], p[64], p[96]);
+    }
+    __device__ __forceinline__ void obs_uniforms(float u[6]) const {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) u[i] = s[(28 + i) * 32];
+    }
+};
+template <bool NOISE>
+__device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCfg& cfg, float* scratch, StepDraws& sd) {
+    sd.s = scratch;
+    sd.ubox0 = sd.ubox1 = 0.0f;
+    sd.r0 = dw.z(cfg, 0);
+    sd.r3 = dw.z(cfg, 3);
+    if (NOISE) {
+        sd.r1 = dw.z(cfg, 1); sd.r2 = dw.z(cfg, 2);
+#pragma unroll
+        for (int b = 4; b < 11; ++b) {
+            float4 v = dw.z(cfg, b);
+            float* p = scratch + (4 * (b - 4)) * 32;
+            p[0] = v.x; p[32] = v.y; p[64] = v.z; p[96] = v.w;
+        }
+        float4 u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
+        scratch[28 * 32] = u0.x; scratch[29 * 32] = u0.y; scratch[30 * 32] = u0.z; scratch[31 * 32] = u0.w;
+        scratch[32 * 32] = u1.x; scratch[33 * 32] = u1.y;
+        sd.ubox0 = u1.z; sd.ubox1 = u1.w;
+    } else {
+        sd.r1 = sd.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 v = dw.z(cfg, 4);                            // only z[16] (OU, substep 2) is live without sensor noise
+        scratch[0] = v.x; scratch[32] = v.y; scratch[64] = v.z; scratch[96] = v.w;
+        if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) { float4 u1 = dw.u(cfg, 1); sd.ubox0 = u1.z; sd.ubox1 = u1.w; }
+    }
+}
+
 struct StepOut {
     float rew, cost, ep_ret;
     int done, truncated, ep_len;
@@ -635,24 +768,25 @@ struct StepOut {
 // e: dynamic words (shared memory in the step kernel); p: the env's domain-randomised parameters.
 template <bool NOISE, int HJ_MODE>
 __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, const DevCfg& cfg, const DevTables& tab,
-                                            const float* thr, const float a[4], const DrawSrc& dw, float* row) {
+                                            const float* thr, const float a[4], const StepDraws& dw, float* row,
+                                            unsigned wmask) {
     constexpr int OD = NOISE ? 34 : 42;
     const uint32_t misc = e.u(CF_S_MISC);
     const int ep_len = (int)e.u(CF_S_EP_LEN);
     Body b;
     e.get4(CF_S_QUAT, b.quat); e.get3(CF_S_OMEGA_W, b.ow);
     // disturbance, once per control step: start the table gather first, the motor model hides its latency
-    int bits = 0;
+    HjFetch hjf;
+    hjf.raw = 0u; hjf.shift = 0;
     const int level = misc_level(misc);
     const bool hj = (cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0;
     float R[9], wb[3];
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame of the pre-step state: HJ lookup and substep 1
-    if (hj) bits = hj_disturbance_bits<HJ_MODE>(b.quat, wb, cfg, tab, thr, level);
+    if (hj) hjf = hj_disturbance_issue<HJ_MODE>(b.quat, wb, cfg, tab, thr, level);
     float d0 = 0.0f, d1 = 0.0f;
     if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {                // dstb_space.sample(), hover_free.py:868-878
-        float4 ub = dw.u(cfg, 1);
-        d0 = unif(-1e-3f, 1e-3f, ub.z);
-        d1 = unif(-1e-3f, 1e-3f, ub.w);
+        d0 = unif(-1e-3f, 1e-3f, dw.ubox0);
+        d1 = unif(-1e-3f, 1e-3f, dw.ubox1);
     }
     e.get3(CF_S_POS, b.pos); e.get3(CF_S_VEL, b.vel); e.get4(CF_S_MOTOR_X, b.x); e.get4(CF_S_OU, b.ou);
     // latency ring (agents.py:268-276): substep 1 reads slot ring_idx, substep 2 the other one; both
@@ -664,32 +798,28 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     const float invm = frcp(p.mass);
     float bias[3], lpf[3];
     if (NOISE) { e.get3(CF_S_GYRO_BIAS, bias); e.get3(CF_S_LPF, lpf); }
-    float4 zq = dw.z(cfg, 0);
-    if (hj) {
-        float dmax = ((float)level / 10.0f) * 5.3e-3f;      // distur_gener.py:152,160
-        d0 = (bits & 1) ? -dmax : dmax;
-        d1 = (bits & 2) ? -dmax : dmax;
-    }
+    float4 zq = dw.z<0>();
+    const float dmax = ((float)level / 10.0f) * 5.3e-3f;     // distur_gener.py:152,160
     // substeps; the reference calls compute_observation() after each (base.py:494-501): only its
     // gyro sample survives (bias walk + low-pass), the rest of that call is overwritten below
     {
         const float zou[4] = {zq.x, zq.y, zq.z, zq.w};
-        physics_substep(b, R, wb, p, invJ, invm, cfg, del1, d0, d1, zou);
+        physics_substep<true>(b, R, wb, p, invJ, invm, cfg, del1, d0, d1, zou, hjf, hj, dmax);
     }
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame after substep 1: gyro sample and substep 2
     float4 z3;
     if (NOISE) {
-        float4 z1 = dw.z(cfg, 1), z2 = dw.z(cfg, 2);
-        z3 = dw.z(cfg, 3);
+        float4 z1 = dw.z<1>(), z2 = dw.z<2>();
+        z3 = dw.z<3>();
         const float zb[3] = {z1.x, z1.y, z1.z}, zr[3] = {z1.w, z2.x, z2.y}, zt[3] = {z2.z, z2.w, z3.x};
         gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
     } else {
-        z3 = dw.z(cfg, 3);
+        z3 = dw.z<3>();
     }
-    float4 z4 = dw.z(cfg, 4);
+    float4 z4 = dw.z<4>();
     {
         const float zou[4] = {z3.y, z3.z, z3.w, z4.x};
-        physics_substep(b, R, wb, p, invJ, invm, cfg, del2, d0, d1, zou);
+        physics_substep<false>(b, R, wb, p, invJ, invm, cfg, del2, d0, d1, zou, hjf, hj, dmax);
     }
     // final rigid-body state back to the tile; true attitude and body rates (agents.py:434-453)
     e.set3(CF_S_POS, b.pos); e.set4(CF_S_QUAT, b.quat); e.set3(CF_S_VEL, b.vel); e.set3(CF_S_OMEGA_W, b.ow);
@@ -714,15 +844,16 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
 #pragma unroll
     for (int i = 0; i < 13; ++i) hist[i] = e.f(CF_S_OBS_PREV + i);
     if (NOISE) {
-        float4 z5 = dw.z(cfg, 5), z6 = dw.z(cfg, 6);
+        float4 z5 = dw.z<5>(), z6 = dw.z<6>();
         {
             const float zb[3] = {z4.y, z4.z, z4.w}, zr[3] = {z5.x, z5.y, z5.z}, zt[3] = {z5.w, z6.x, z6.y};
             gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
         }
-        float4 z7 = dw.z(cfg, 7), z8 = dw.z(cfg, 8), z9 = dw.z(cfg, 9), z10 = dw.z(cfg, 10), u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
+        float4 z7 = dw.z<7>(), z8 = dw.z<8>(), z9 = dw.z<9>(), z10 = dw.z<10>();
         const float z[18] = {z6.z, z6.w, z7.x, z7.y, z7.z, z7.w, z8.x, z8.y, z8.z, z8.w, z9.x, z9.y, z9.z, z9.w,
                              z10.x, z10.y, z10.z, z10.w};
-        const float u[6] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y};
+        float u[6];
+        dw.obs_uniforms(u);
         float on[13];
         observe_full(b.pos, b.vel, rpy, wb, bias, lpf, cfg, z, u, on);
         e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
@@ -741,6 +872,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
 #pragma unroll
         for (int i = 0; i < 4; ++i) { hist[24 + i] = b.quat[i]; e.f(CF_S_OBS_PREV + 3 + i, b.quat[i]); }
     }
+    __syncwarp(wmask);                                      // every lane has read its draws: the rows may overwrite the scratch
     store_row<OD>(row, hist);
     // compute_done (hover_free.py:449-461), reward (hover_free.py:206-235 / hover.py:184-202),
     // cost (hover_free.py:138-166) on the TRUE state

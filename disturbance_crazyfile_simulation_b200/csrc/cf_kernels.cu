@@ -89,46 +89,69 @@ __device__ __forceinline__ void copy_row(float* __restrict__ dst, const float* s
 #endif
 
 // env.step for all envs, `k` control steps per launch with the tile's state held in shared memory.
-// Envs that finish an episode are reset in place after the tile's step phase: the CTA's warps share
-// the tile's finished envs; for each, 23 lanes produce the 23 Philox blocks of the reset event in
-// parallel into shared memory and lane 0 runs the (short) serial part - the reset leaves the
-// critical path of the warp that happened to own the env.
+// Timeline of a CTA: (1) thread 0 starts the bulk copy of the state tile; every thread fetches its event
+// counter, action and domain-randomised parameters with ordinary loads and produces ALL standard draws of
+// the step (Philox + Box-Muller, ~40 % of the step's instructions) while the tile is in flight; (2) the step
+// runs against shared memory; (3) envs that finished an episode are reset in place by the whole CTA: up to
+// four at a time, 23 threads per env generate the reset's Philox blocks, then the reset's independent tasks
+// (pose / parameters, the two observations, action history) run on different warps with one env per lane;
+// (4) the tile's state and observation rows leave with one bulk copy each.
 template <bool NOISE, int HJ_MODE>
 __global__ void __launch_bounds__(CF_TILE, CF_MIN_CTAS)
 k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, const __grid_constant__ DevTables tab,
        const __grid_constant__ StepIO io) {
     constexpr int OD = NOISE ? 34 : 42;
     constexpr int NW = CF_TILE / 32;
+    constexpr int RC = 4;                                   // finished envs reset concurrently (RC * 23 <= 96 threads)
+    constexpr bool kParallelReset = NOISE && NW >= 4;
     constexpr uint32_t kStateBytes = CF_DYN_WORDS * CF_TILE * 4, kObsBytes = OD * CF_TILE * 4;
     extern __shared__ __align__(128) float smem[];
     float* s_state = smem;                                  // [60][CF_TILE]
-    float* s_obs = s_state + CF_DYN_WORDS * CF_TILE;        // [CF_TILE][OD]
+    float* s_obs = s_state + CF_DYN_WORDS * CF_TILE;        // [CF_TILE][OD]; before the rows are written: draw scratch
     float* s_thr = s_obs + OD * CF_TILE;                    // [6][16]
-    float* s_draw = s_thr + 96;                             // [NW][96] reset draws of the env a warp is resetting
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_draw + NW * 96);
+    float* s_draw = s_thr + 96;                             // [RC][96] reset draws (z[48], u[44]) of the envs being reset
+    float* s_ctx = s_draw + RC * 96;                        // [RC][32] ResetCtx of the envs being reset
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_ctx + RC * 32);
     int* s_ndone = reinterpret_cast<int*>(mbar + 1);        // [2]
     uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x, i = tile * CF_TILE + tid;
     float* gtile = S + (size_t)tile * (CF_STATE_WORDS * CF_TILE);
     const bool valid = i < n;
+    const unsigned wmask = __ballot_sync(0xffffffffu, valid);
     const bool bulk_obs = io.bulk_obs && (tile + 1) * CF_TILE <= n;
     unsigned long long* tr = io.trace ? io.trace + CF_TRACE_WORDS * (size_t)tile : nullptr;    // per-CTA timeline (debug)
     if (tr && tid == 0) { tr[0] = smid(); tr[1] = gtimer(); }
+    // the event counter first (the draws wait for it), then the tile: it should not queue behind 15 MB of bulk copies
+    const uint32_t ctr0 = __float_as_uint(__ldcg(gtile + CF_S_RNG_CTR * CF_TILE + tid));
     if (tid == 0) {
         s_ndone[0] = 0;
         mbar_init(mbar, 1);
         mbar_arrive_expect_tx(mbar, kStateBytes);
+#ifdef CF_STAGGER
+        uint32_t z;                                         // the tile is requested once the counter has arrived (counter < 2^31)
+        asm volatile("shr.u32 %0, %1, 31;" : "=r"(z) : "r"(ctr0));
+        bulk_g2s(s_state, gtile + 4 * z, kStateBytes, mbar);
+#else
         bulk_g2s(s_state, gtile, kStateBytes, mbar);
+#endif
     }
-    if (tid < 96) s_thr[tid] = __ldg(tab.thr + tid);
     const EnvRef e{s_state + tid};
     const EnvRef g{gtile + tid};
-    DrParams p;
-    p.load(g);                                              // coalesced loads, in flight with the bulk copy
     float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) av = __ldg(reinterpret_cast<const float4*>(io.act) + i);
+    if (tid < 96) s_thr[tid] = __ldg(tab.thr + tid);
+    DrParams p;
+    p.load(g);                                              // coalesced loads, in flight with the bulk copy
     const long long gid = cfg.gid_base + i;
     float* row = s_obs + tid * OD;
+    float* scratch = s_obs + warp * (32 * OD) + lane;
+    StepDraws sd;
+    if (tr && tid == 0) { asm volatile("" :: "r"(ctr0)); tr[12] = gtimer(); }
+    if (valid) {                                            // step event of this launch's first step: counter ctr0, tag 0
+        const DrawSrc dw = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
+        pregen_step_draws<NOISE>(dw, cfg, scratch, sd);
+    }
+    if (tr && tid == 0) tr[11] = gtimer();
     __syncthreads();                                        // mbarrier initialised, thresholds in place
     mbar_wait(mbar, 0);
     if (tr && tid == 0) tr[2] = gtimer();
@@ -138,12 +161,14 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         const size_t r = (size_t)t * n + i;
         bool my_reset = false;
         if (valid) {
-            if (t > 0) av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
+            if (t > 0) {
+                av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
+                const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
+                pregen_step_draws<NOISE>(dw, cfg, scratch, sd);
+            }
             const float a[4] = {av.x, av.y, av.z, av.w};
-            const uint32_t ctr = e.u(CF_S_RNG_CTR);          // step event: counter before the increment, tag 0;
-            e.u(CF_S_RNG_CTR, ctr + 1u);                    // an in-place reset in this launch: counter after it, tag 1
-            const DrawSrc dw = make_draws(cfg, gid, ctr, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, s_thr, a, dw, row);
+            e.u(CF_S_RNG_CTR, ctr0 + (uint32_t)t + 1u);     // an in-place reset in this launch: counter after the step, tag 1
+            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, s_thr, a, sd, row, wmask);
             io.rew[r] = so.rew;
             io.done[r] = (uint8_t)so.done;
             if (io.cost) io.cost[r] = so.cost;
@@ -168,24 +193,68 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         if (tr && tid == 0 && t == 0) tr[7] = gtimer();
         const int nd = s_ndone[0];
         if (nd > 0) {                                       // uniform over the CTA
-            for (int j = warp; j < nd; j += NW) {
-                const int et = s_list[j];
-                const EnvRef ee{s_state + et};
-                const EnvRef gg{gtile + et};
-                float* zs = s_draw + warp * 96;
-                float* us = zs + CF_RESET_NORMALS;
-                const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
-                                              io.inj_reset_u, n, tile * CF_TILE + et, CF_RESET_UNIFORMS);
-                if (lane < 12) {
-                    float4 v = dr.z(cfg, lane);
-                    zs[4 * lane] = v.x; zs[4 * lane + 1] = v.y; zs[4 * lane + 2] = v.z; zs[4 * lane + 3] = v.w;
-                } else if (lane < 23) {
-                    float4 v = dr.u(cfg, lane - 12);
-                    us[4 * (lane - 12)] = v.x; us[4 * (lane - 12) + 1] = v.y; us[4 * (lane - 12) + 2] = v.z; us[4 * (lane - 12) + 3] = v.w;
+            if (kParallelReset) {
+                for (int c0 = 0; c0 < nd; c0 += RC) {
+                    const int cnt = min(RC, nd - c0);
+                    // R1: the reset events' draws (23 Philox blocks per env, one thread each) + what is read from the old state
+                    if (tid < 23 * cnt) {
+                        const int j = tid / 23, b = tid - 23 * j, et = s_list[c0 + j];
+                        const EnvRef ee{s_state + et};
+                        const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
+                                                      io.inj_reset_u, n, tile * CF_TILE + et, CF_RESET_UNIFORMS);
+                        float4 v;
+                        float* dst;
+                        if (b < 12) { v = dr.z(cfg, b); dst = s_draw + j * 96 + 4 * b; }
+                        else { v = dr.u(cfg, b - 12); dst = s_draw + j * 96 + CF_RESET_NORMALS + 4 * (b - 12); }
+                        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+                    } else if (tid >= 96 && tid < 96 + cnt) {
+                        const int j = tid - 96;
+                        ResetCtx* c = reinterpret_cast<ResetCtx*>(s_ctx + j * 32);
+                        reset_task_stale(EnvRef{s_state + s_list[c0 + j]}, *c);
+                    }
+                    __syncthreads();
+                    // R2, one env per lane: pose + motor state (warp 0) | domain randomisation, counters, level (warp 1) |
+                    // gyro-free part of the first (warp 2) and second (warp 3) observation + action history
+                    if (lane < cnt) {
+                        const int et = s_list[c0 + lane];
+                        const float* zs = s_draw + lane * 96;
+                        const float* us = zs + CF_RESET_NORMALS;
+                        const EnvRef ee{s_state + et};
+                        float* rw = s_obs + et * OD;
+                        if (warp == 0) reset_task_pose(ee, cfg, zs, us, reinterpret_cast<ResetCtx*>(s_ctx + lane * 32)->wb);
+                        else if (warp == 1) reset_task_params(ee, EnvRef{gtile + et}, cfg, us);
+                        else if (warp == 2) reset_task_obs_nongyro<0>(ee, cfg, zs, us, rw);
+                        else reset_task_obs_nongyro<1>(ee, cfg, zs, us, rw);
+                    }
+                    __syncthreads();
+                    // R3: the gyro samples of both observations (need the new body rate and the old gyro state)
+                    if (warp == 0 && lane < cnt) {
+                        const int et = s_list[c0 + lane];
+                        reset_task_gyro(EnvRef{s_state + et}, *reinterpret_cast<const ResetCtx*>(s_ctx + lane * 32), cfg,
+                                        s_draw + lane * 96, s_obs + et * OD);
+                    }
+                    if (c0 + RC < nd) __syncthreads();      // the scratch is reused by the next group
                 }
-                __syncwarp();
-                if (lane == 0) reset_env<NOISE>(ee, gg, cfg, zs, us, s_obs + et * OD);
-                __syncwarp();
+            } else {
+                for (int j = warp; j < nd; j += NW) {       // one env per warp: 23 lanes draw, lane 0 resets
+                    const int et = s_list[j];
+                    const EnvRef ee{s_state + et};
+                    const EnvRef gg{gtile + et};
+                    float* zs = s_draw + (warp % RC) * 96;
+                    float* us = zs + CF_RESET_NORMALS;
+                    const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
+                                                  io.inj_reset_u, n, tile * CF_TILE + et, CF_RESET_UNIFORMS);
+                    if (lane < 12) {
+                        float4 v = dr.z(cfg, lane);
+                        zs[4 * lane] = v.x; zs[4 * lane + 1] = v.y; zs[4 * lane + 2] = v.z; zs[4 * lane + 3] = v.w;
+                    } else if (lane < 23) {
+                        float4 v = dr.u(cfg, lane - 12);
+                        us[4 * (lane - 12)] = v.x; us[4 * (lane - 12) + 1] = v.y; us[4 * (lane - 12) + 2] = v.z; us[4 * (lane - 12) + 3] = v.w;
+                    }
+                    __syncwarp();
+                    if (lane == 0) reset_env<NOISE>(ee, gg, cfg, zs, us, s_obs + et * OD);
+                    __syncwarp();
+                }
             }
             total_done += nd;
             fence_async_smem();
@@ -209,7 +278,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                 bulk_wait_read();
             }
         }
-        if (t + 1 < k) __syncthreads();                     // rows may be overwritten by the next step
+        if (t + 1 < k) __syncthreads();                     // rows may be overwritten by the next step's draws
     }
     if (tr && tid == 0) { tr[9] = gtimer(); tr[10] = (unsigned long long)total_done; }
 }
@@ -325,7 +394,7 @@ void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float
 }
 
 size_t step_smem_bytes(int obs_dim) {
-    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + (CF_TILE / 32) * 96 * 4 + 8 + 8 + CF_TILE;
+    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + 4 * 96 * 4 + 4 * 32 * 4 + 8 + 8 + CF_TILE;
 }
 
 template <bool NOISE, int HJ_MODE>

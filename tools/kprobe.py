@@ -103,10 +103,10 @@ def main():
         T = tr.cpu().numpy()
         t0 = T[:, 1].min()
         us_ = lambda c: (T[:, c] - t0) / 1e3
-        start, landed, b1, b2, end = us_(1), us_(2), us_(7), us_(8), us_(9)
+        start, landed, b1, b2, end, drawn = us_(1), us_(2), us_(7), us_(8), us_(9), us_(11)
         wfin = np.stack([us_(3 + w) for w in range(4)], axis=1)
         nd = T[:, 10]
-        print(f'--- trace {rep}: kernel span {end.max():.2f} us | CTA start spread {start.max():.2f} | landed median {np.median(landed):.2f} '
+        print(f'--- trace {rep}: kernel span {end.max():.2f} us | CTA start spread {start.max():.2f} | ctr landed median {np.median(us_(12)):.2f} max {us_(12).max():.2f} | draws done median {np.median(drawn):.2f} max {drawn.max():.2f} | landed median {np.median(landed):.2f} '
               f'max {landed.max():.2f} | warp step phase (from landed) median {np.median(wfin - landed[:, None]):.2f} '
               f'p99 {np.percentile(wfin - landed[:, None], 99):.2f} max {(wfin - landed[:, None]).max():.2f} | '
               f'barrier1 median {np.median(b1):.2f} max {b1.max():.2f} | reset phase median {np.median((b2 - b1)[nd > 0]) if (nd > 0).any() else 0:.2f} '
