@@ -51,6 +51,8 @@ def parse():
     ap.add_argument('--streams', type=int, default=1,
                     help='independent shards are stepped on this many streams (parallel branches of the CUDA graph), so one '
                          "shard's load/store phases overlap another's compute")
+    ap.add_argument('--no-prefetch', action='store_true',
+                    help='do not chain the shards with cf_set_prefetch_next (each step kernel asks the L2 to prefetch the next shard)')
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
@@ -202,6 +204,9 @@ def main_ours(args):
 
     for e in shards:
         e.reset()
+    if not args.no_prefetch and S > 1:
+        for i in range(S):                               # shard i's step kernel prefetches shard i+1's state and actions into L2
+            shards[i].set_prefetch_next(shards[(i + NS) % S], acts[(i + NS) % S])   # the shard this stream steps next
 
     def run(k_steps, offset=0):
         """k_steps control steps, shard (offset+t) % S on stream t % NS (fork / join around the batch)"""
@@ -281,6 +286,20 @@ def main_ours(args):
         e0.step_k(actk, obsk, rewk, donek, costk)
     ev1.record(); torch.cuda.synchronize()
     side[f'fused_k{kf}_env_steps_per_s'] = n * kf * 5 / (ev0.elapsed_time(ev1) * 1e-3)
+    # (c) fused GAE pass (cf_gae_dev) over a [T][N] rollout buffer larger than L2: 21 algorithmic bytes per sample
+    from disturbance_crazyfile_simulation_b200.gae import gae
+    Tg, Ng = 32, 8 * n
+    g_rew = torch.randn((Tg, Ng), device=dev); g_val = torch.randn((Tg, Ng), device=dev)
+    g_done = (torch.rand((Tg, Ng), device=dev) < 0.01).to(torch.uint8); g_last = torch.randn(Ng, device=dev)
+    gae(g_rew, g_val, g_done, None, g_last)
+    ev0.record()
+    for _ in range(5):
+        gae(g_rew, g_val, g_done, None, g_last)
+    ev1.record(); torch.cuda.synchronize()
+    gae_ms = ev0.elapsed_time(ev1) / 5
+    side['gae'] = {'T': Tg, 'N': Ng, 'ms': gae_ms, 'samples_per_s': Tg * Ng / (gae_ms * 1e-3),
+                   'achieved_gb_s': 21 * Tg * Ng / (gae_ms * 1e-3) / 1e9, 'bytes_per_sample': 21}
+    del g_rew, g_val, g_done, g_last
     stats = e0.episode_stats()
     side['mean_episode_length_shard0'] = stats['mean_length']
 
@@ -325,7 +344,10 @@ def main_ours(args):
                        'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
                                     'packed 2-bit sign tables in HBM/L2',
                        'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S} (one per shard)')
-                                    + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else '')},
+                                    + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else ''),
+                       'shard_pipelining': ('off' if args.no_prefetch or S == 1 else
+                                            'each step kernel issues cp.async.bulk.prefetch.L2 for the state + actions of the shard stepped next '
+                                            '(cf_set_prefetch_next); every byte still comes from HBM once per step')},
             'clocks': clocks, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
                     'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,

@@ -88,6 +88,7 @@ _SIGS = {
     'cf_episode_stats': (C.c_int, [_P, C.c_int32, _P, _P, _P]),
     'cf_gae_dev': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P, _P]),
     'cf_gae_host': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P]),
+    'cf_set_prefetch_next': (C.c_int, [_P, _P, _P]),
     'cf_set_trace_buffer': (C.c_int, [_P, _P]),
     'cf_num_tiles': (C.c_int, [_P]),
     'cf_launch_count': (C.c_int64, [_P]),

@@ -61,6 +61,8 @@ struct cf_env {
     bool tables_borrowed = false;    // tables belong to another handle (cf_share_hj_tables)
     long long launches = 0;
     unsigned long long* trace = nullptr;   // caller-owned device buffer (cf_set_trace_buffer)
+    const cf_env* pf_next = nullptr;       // cf_set_prefetch_next
+    const float* pf_act = nullptr;
     bool timing = false;
     std::vector<EventPair> ev_pool;
     size_t ev_used = 0;
@@ -206,6 +208,9 @@ int derive(const cf_config& c, uint64_t seed, int64_t gid_base, DevCfg& d) {
         double grid[6][CF_HJ_PTS], dx[6], cdf[21];
         grid_tables(grid, dx, cdf);
         for (int k = 0; k < 6; ++k) { d.hj_lo[k] = (float)grid[k][0]; d.hj_inv_dx[k] = (float)(1.0 / dx[k]); }
+        float thr[6][16];
+        index_thresholds(grid, thr);
+        memcpy(d.hj_thr, thr, sizeof(thr));
         for (int k = 0; k < 20; ++k) {                      // smallest float32 t with cdf[k] <= (double)t
             float t = (float)cdf[k];
             if ((double)t < cdf[k]) t = nextafterf(t, INFINITY);
@@ -269,6 +274,8 @@ int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint
     io.fin_ret = e->fin_ret; io.fin_len = e->fin_len; io.agg = e->agg;
     // a full tile's observation rows leave with one bulk copy when every tile's first row is 16-byte aligned
     io.trace = e->trace;
+    io.pf_S = e->pf_next ? e->pf_next->S : nullptr; io.pf_act = e->pf_next ? e->pf_act : nullptr;
+    io.pf_tiles = e->pf_next ? e->pf_next->n_pad / CF_TILE : 0; io.pf_n = e->pf_next ? e->pf_next->n : 0;
     io.bulk_obs = ((uintptr_t)obs % 16 == 0) && (k == 1 || ((size_t)e->n * e->obs_dim * 4) % 16 == 0);
     if ((uintptr_t)act % 16 != 0) return fail(CF_ERR_INVALID, "cf_step: act must be 16-byte aligned%s", "");
     if ((uintptr_t)obs % 8 != 0 || (term_obs && (uintptr_t)term_obs % 8 != 0))
@@ -638,6 +645,15 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
     if (err == cudaSuccess) err = cudaMemcpy(disc_ret, d_ret, sizeof(float) * tn, cudaMemcpyDeviceToHost);
     cudaFree(d_f); cudaFree(d_d);
     if (err != cudaSuccess) return cuda_fail(err, "cf_gae_host");
+    return CF_OK;
+}
+
+int cf_set_prefetch_next(cf_env* e, const cf_env* next, const float* next_act) {
+    if (!e) return fail(CF_ERR_INVALID, "cf_set_prefetch_next: null handle%s", "");
+    if (next && next->device != e->device) return fail(CF_ERR_INVALID, "cf_set_prefetch_next: handles must be on the same device%s", "");
+    if (next_act && (uintptr_t)next_act % 16 != 0) return fail(CF_ERR_INVALID, "cf_set_prefetch_next: next_act must be 16-byte aligned%s", "");
+    e->pf_next = next;
+    e->pf_act = next ? next_act : nullptr;
     return CF_OK;
 }
 

@@ -729,30 +729,53 @@ struct StepDraws {
         for (int i = 0; i < 6; ++i) u[i] = s[(28 + i) * 32];
     }
 };
-template <bool NOISE>
+// PART 0: blocks 0..5 (+ the random-box uniforms); PART 1: blocks 6..10 and the observation uniforms.  The step
+// kernel runs part 0 while the tile is in flight and part 1 behind the HJ table gather.
+template <bool NOISE, int PART>
 __device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCfg& cfg, float* scratch, StepDraws& sd) {
-    sd.s = scratch;
-    sd.ubox0 = sd.ubox1 = 0.0f;
-    sd.r0 = dw.z(cfg, 0);
-    sd.r3 = dw.z(cfg, 3);
+    if (PART == 0) {
+        sd.s = scratch;
+        sd.ubox0 = sd.ubox1 = 0.0f;
+        sd.r0 = dw.z(cfg, 0);
+        sd.r3 = dw.z(cfg, 3);
+        if (NOISE) { sd.r1 = dw.z(cfg, 1); sd.r2 = dw.z(cfg, 2); }
+        else sd.r1 = sd.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     if (NOISE) {
-        sd.r1 = dw.z(cfg, 1); sd.r2 = dw.z(cfg, 2);
 #pragma unroll
-        for (int b = 4; b < 11; ++b) {
+        for (int b = (PART == 0 ? 4 : 6); b < (PART == 0 ? 6 : 11); ++b) {
             float4 v = dw.z(cfg, b);
             float* p = scratch + (4 * (b - 4)) * 32;
             p[0] = v.x; p[32] = v.y; p[64] = v.z; p[96] = v.w;
         }
-        float4 u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
-        scratch[28 * 32] = u0.x; scratch[29 * 32] = u0.y; scratch[30 * 32] = u0.z; scratch[31 * 32] = u0.w;
-        scratch[32 * 32] = u1.x; scratch[33 * 32] = u1.y;
-        sd.ubox0 = u1.z; sd.ubox1 = u1.w;
-    } else {
-        sd.r1 = sd.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (PART == 1) {
+            float4 u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
+            scratch[28 * 32] = u0.x; scratch[29 * 32] = u0.y; scratch[30 * 32] = u0.z; scratch[31 * 32] = u0.w;
+            scratch[32 * 32] = u1.x; scratch[33 * 32] = u1.y;
+        } else if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {
+            float4 u1 = dw.u(cfg, 1);
+            sd.ubox0 = u1.z; sd.ubox1 = u1.w;
+        }
+    } else if (PART == 0) {
         float4 v = dw.z(cfg, 4);                            // only z[16] (OU, substep 2) is live without sensor noise
         scratch[0] = v.x; scratch[32] = v.y; scratch[64] = v.z; scratch[96] = v.w;
         if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) { float4 u1 = dw.u(cfg, 1); sd.ubox0 = u1.z; sd.ubox1 = u1.w; }
     }
+}
+
+// The HJ table fetch of a step, issued from the tile as soon as it has landed (step_env consumes it).
+template <int HJ_MODE>
+__device__ __forceinline__ HjFetch step_issue_hj(const EnvRef e, const DevCfg& cfg, const DevTables& tab, const float* thr) {
+    HjFetch f;
+    f.raw = 0u; f.shift = 0;
+    const int level = misc_level(e.u(CF_S_MISC));
+    if ((cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0) {
+        float q[4], ow[3], R[9], wb[3];
+        e.get4(CF_S_QUAT, q); e.get3(CF_S_OMEGA_W, ow);
+        quat_to_R(q, R); matTvec(R, ow, wb);
+        f = hj_disturbance_issue<HJ_MODE>(q, wb, cfg, tab, thr, level);
+    }
+    return f;
 }
 
 struct StepOut {
@@ -768,7 +791,7 @@ struct StepOut {
 // e: dynamic words (shared memory in the step kernel); p: the env's domain-randomised parameters.
 template <bool NOISE, int HJ_MODE>
 __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, const DevCfg& cfg, const DevTables& tab,
-                                            const float* thr, const float a[4], const StepDraws& dw, float* row,
+                                            const HjFetch& hjf, const float a[4], const StepDraws& dw, float* row,
                                             unsigned wmask) {
     constexpr int OD = NOISE ? 34 : 42;
     const uint32_t misc = e.u(CF_S_MISC);
@@ -776,13 +799,10 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     Body b;
     e.get4(CF_S_QUAT, b.quat); e.get3(CF_S_OMEGA_W, b.ow);
     // disturbance, once per control step: start the table gather first, the motor model hides its latency
-    HjFetch hjf;
-    hjf.raw = 0u; hjf.shift = 0;
     const int level = misc_level(misc);
     const bool hj = (cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0;
     float R[9], wb[3];
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame of the pre-step state: HJ lookup and substep 1
-    if (hj) hjf = hj_disturbance_issue<HJ_MODE>(b.quat, wb, cfg, tab, thr, level);
     float d0 = 0.0f, d1 = 0.0f;
     if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {                // dstb_space.sample(), hover_free.py:868-878
         d0 = unif(-1e-3f, 1e-3f, dw.ubox0);

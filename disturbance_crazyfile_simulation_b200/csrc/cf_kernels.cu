@@ -41,6 +41,10 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                  ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
 }
+// hint: bring [p, p + bytes) into the L2 (16-byte aligned, 16-byte multiple); no completion to wait for
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 // make generic-proxy shared-memory writes visible to the async proxy (before a bulk store reads them)
@@ -102,8 +106,9 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
        const __grid_constant__ StepIO io) {
     constexpr int OD = NOISE ? 34 : 42;
     constexpr int NW = CF_TILE / 32;
-    constexpr int RC = 4;                                   // finished envs reset concurrently (RC * 23 <= 96 threads)
-    constexpr bool kParallelReset = NOISE && NW >= 4;
+    constexpr int RC = CF_TILE >= 128 ? 4 : 2;              // finished envs reset concurrently: 23 threads each for the draws + 1
+    constexpr bool kParallelReset = NOISE && NW >= 2;
+    static_assert(!kParallelReset || 24 * RC <= CF_TILE, "reset groups");
     constexpr uint32_t kStateBytes = CF_DYN_WORDS * CF_TILE * 4, kObsBytes = OD * CF_TILE * 4;
     extern __shared__ __align__(128) float smem[];
     float* s_state = smem;                                  // [60][CF_TILE]
@@ -139,23 +144,30 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     const EnvRef g{gtile + tid};
     float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) av = __ldg(reinterpret_cast<const float4*>(io.act) + i);
-    if (tid < 96) s_thr[tid] = __ldg(tab.thr + tid);
+    for (int q = tid; q < 96; q += CF_TILE) s_thr[q] = cfg.hj_thr[q];               // from the constant bank: no global load in front of the HJ lookup
     DrParams p;
     p.load(g);                                              // coalesced loads, in flight with the bulk copy
     const long long gid = cfg.gid_base + i;
     float* row = s_obs + tid * OD;
     float* scratch = s_obs + warp * (32 * OD) + lane;
     StepDraws sd;
-    if (tr && tid == 0) { asm volatile("" :: "r"(ctr0)); tr[12] = gtimer(); }
-    if (valid) {                                            // step event of this launch's first step: counter ctr0, tag 0
-        const DrawSrc dw = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-        pregen_step_draws<NOISE>(dw, cfg, scratch, sd);
+    if (tr && tid == 0) {
+        asm volatile("" :: "r"(ctr0)); tr[12] = gtimer();
     }
-    if (tr && tid == 0) tr[11] = gtimer();
     __syncthreads();                                        // mbarrier initialised, thresholds in place
+    DrawSrc dw0 = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
+    if (valid) pregen_step_draws<NOISE, 0>(dw0, cfg, scratch, sd);   // step event of the launch's first step: counter ctr0, tag 0
+    if (tr && tid == 0) tr[11] = gtimer();
     mbar_wait(mbar, 0);
     if (tr && tid == 0) tr[2] = gtimer();
-    if (valid) consume_fresh(e, cfg, gid, NOISE);
+    HjFetch hjf;
+    hjf.raw = 0u; hjf.shift = 0;
+    if (valid) {
+        consume_fresh(e, cfg, gid, NOISE);
+        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr);   // the table gather is in flight behind the second half of the draws
+        pregen_step_draws<NOISE, 1>(dw0, cfg, scratch, sd);
+    }
+    if (tr && tid == 0) tr[13] = gtimer();
     int total_done = 0;
     for (int t = 0; t < k; ++t) {
         const size_t r = (size_t)t * n + i;
@@ -164,11 +176,22 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (t > 0) {
                 av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
                 const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-                pregen_step_draws<NOISE>(dw, cfg, scratch, sd);
+                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr);
+                pregen_step_draws<NOISE, 0>(dw, cfg, scratch, sd);
+                pregen_step_draws<NOISE, 1>(dw, cfg, scratch, sd);
             }
             const float a[4] = {av.x, av.y, av.z, av.w};
             e.u(CF_S_RNG_CTR, ctr0 + (uint32_t)t + 1u);     // an in-place reset in this launch: counter after the step, tag 1
-            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, s_thr, a, sd, row, wmask);
+            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, hjf, a, sd, row, wmask);
+            // this warp's table gather has been consumed: HBM may now stream in the inputs of the handle stepped next
+            // (cf_set_prefetch_next); each warp asks for a quarter of the CTA's share
+            if (io.pf_S && lane == 0 && t == 0) {
+                constexpr uint32_t kQ = CF_STATE_WORDS * CF_TILE * 4 / NW;
+                for (int pt = tile; pt < io.pf_tiles; pt += gridDim.x) {
+                    bulk_prefetch_l2(reinterpret_cast<const char*>(io.pf_S + (size_t)pt * (CF_STATE_WORDS * CF_TILE)) + warp * kQ, kQ);
+                    if (io.pf_act && warp == 0 && (pt + 1) * CF_TILE <= io.pf_n) bulk_prefetch_l2(io.pf_act + (size_t)pt * CF_TILE * 4, CF_TILE * 16);
+                }
+            }
             io.rew[r] = so.rew;
             io.done[r] = (uint8_t)so.done;
             if (io.cost) io.cost[r] = so.cost;
@@ -207,8 +230,8 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         if (b < 12) { v = dr.z(cfg, b); dst = s_draw + j * 96 + 4 * b; }
                         else { v = dr.u(cfg, b - 12); dst = s_draw + j * 96 + CF_RESET_NORMALS + 4 * (b - 12); }
                         dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
-                    } else if (tid >= 96 && tid < 96 + cnt) {
-                        const int j = tid - 96;
+                    } else if (tid >= 23 * RC && tid < 23 * RC + cnt) {
+                        const int j = tid - 23 * RC;
                         ResetCtx* c = reinterpret_cast<ResetCtx*>(s_ctx + j * 32);
                         reset_task_stale(EnvRef{s_state + s_list[c0 + j]}, *c);
                     }
@@ -221,10 +244,14 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         const float* us = zs + CF_RESET_NORMALS;
                         const EnvRef ee{s_state + et};
                         float* rw = s_obs + et * OD;
-                        if (warp == 0) reset_task_pose(ee, cfg, zs, us, reinterpret_cast<ResetCtx*>(s_ctx + lane * 32)->wb);
-                        else if (warp == 1) reset_task_params(ee, EnvRef{gtile + et}, cfg, us);
-                        else if (warp == 2) reset_task_obs_nongyro<0>(ee, cfg, zs, us, rw);
-                        else reset_task_obs_nongyro<1>(ee, cfg, zs, us, rw);
+#pragma unroll
+                        for (int task = 0; task < 4; ++task) {
+                            if (warp >= (NW < 4 ? NW : 4) || task % (NW < 4 ? NW : 4) != warp) continue;
+                            if (task == 0) reset_task_pose(ee, cfg, zs, us, reinterpret_cast<ResetCtx*>(s_ctx + lane * 32)->wb);
+                            else if (task == 1) reset_task_params(ee, EnvRef{gtile + et}, cfg, us);
+                            else if (task == 2) reset_task_obs_nongyro<0>(ee, cfg, zs, us, rw);
+                            else reset_task_obs_nongyro<1>(ee, cfg, zs, us, rw);
+                        }
                     }
                     __syncthreads();
                     // R3: the gyro samples of both observations (need the new body rate and the old gyro state)
@@ -394,7 +421,8 @@ void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float
 }
 
 size_t step_smem_bytes(int obs_dim) {
-    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + 4 * 96 * 4 + 4 * 32 * 4 + 8 + 8 + CF_TILE;
+    const int rc = CF_TILE >= 128 ? 4 : 2;
+    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + rc * 96 * 4 + rc * 32 * 4 + 8 + 8 + CF_TILE;
 }
 
 template <bool NOISE, int HJ_MODE>

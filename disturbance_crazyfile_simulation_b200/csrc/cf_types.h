@@ -40,6 +40,7 @@ struct DevCfg {
     float quat_std, quat_unif;
     float gnd_hclip;
     float hj_lo[6], hj_inv_dx[6];           // grid origin and 1/dx per dim (index guess, float32)
+    float hj_thr[96];                       // [6][16] float32 index thresholds (cf_device.cuh hj_index_f32), same as DevTables::thr
     float boltz_thr[20];                    // Boltzmann level draw: smallest float32 >= cdf[k] (envs/utils.py:27-39)
     uint32_t pk[10][2];                     // Philox4x32-10 round keys of the seed
     long long gid_base;
@@ -69,6 +70,9 @@ struct StepIO {
     int* fin_len;          // [n]
     double* agg;           // [CF_AGG_SLOTS][4]: episodes, sum return, sum length, (spare)
     int bulk_obs;          // obs rows of a full tile may leave with one bulk copy (16-byte aligned)
+    const float* pf_S;     // L2 prefetch hint (cf_set_prefetch_next): tiled state of the handle stepped next, or null
+    const float* pf_act;   // its action rows [pf_n][4] or null
+    int pf_tiles, pf_n;
     unsigned long long* trace;   // debug: [n_tiles][CF_TRACE_WORDS] per-CTA timeline (cf_set_trace_buffer) or null
 };
 

@@ -244,6 +244,12 @@ class CrazyFlieVecEnv:
         return {'episodes': int(n), 'return_sum': out[1], 'length_sum': out[2],
                 'mean_return': out[1] / n if n else float('nan'), 'mean_length': out[2] / n if n else float('nan')}
 
+    def set_prefetch_next(self, nxt: Optional['CrazyFlieVecEnv'], next_act: Optional[torch.Tensor] = None) -> None:
+        """Shard pipelining hint: while this env is stepped, prefetch the state of ``nxt`` (the env stepped next
+        on this GPU) and its action rows into the L2.  Results never depend on it; ``None`` switches it off."""
+        self._pf_keep = (nxt, next_act)              # keep both alive while the hint is set
+        abi.check(self._L.cf_set_prefetch_next(self._h, None if nxt is None else nxt._h, _ptr(next_act)))
+
     def kernel_timing(self, enable: bool, reset: bool = False):
         ms, cnt = C.c_double(), C.c_int64()
         abi.check(self._L.cf_kernel_timing(self._h, int(enable), int(reset), C.byref(ms), C.byref(cnt)))

@@ -165,6 +165,13 @@ int cf_step_dev(cf_env* env, const float* act, float* obs, float* rew, uint8_t* 
 int cf_step_k_dev(cf_env* env, int32_t k, const float* act, float* obs, float* rew,
                   uint8_t* done, float* cost, void* stream);
 
+/* Shard pipelining hint for callers that step several handles of one GPU in turn (their combined state does not
+ * fit the L2): while `env` is stepped, its step kernel asks the L2 to prefetch the state of `next` (and the
+ * `next_act` rows, [n_next][4], nullable), so that the next handle's step finds its inputs in L2 instead of
+ * waiting for HBM at its start.  A hint only: results never depend on it.  next = NULL switches it off.
+ * `next` must be on the same device and outlive the setting. */
+int cf_set_prefetch_next(cf_env* env, const cf_env* next, const float* next_act);
+
 /* ---- host-pointer API (what a gym-style caller with NumPy buffers uses) -------------- */
 int cf_reset_host(cf_env* env, const uint8_t* mask, float* obs);
 int cf_step_host(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,

@@ -28,6 +28,7 @@ def main():
     ap.add_argument('--traces', type=int, default=3)
     ap.add_argument('--streams', type=int, nargs='*', default=[1])
     ap.add_argument('--graph-reps', type=int, nargs='*', default=[1], help='round-robin passes over the shards captured per graph')
+    ap.add_argument('--prefetch', action='store_true', help='each shard prefetches the next one (cf_set_prefetch_next)')
     ap.add_argument('--kw', nargs='*', default=[])
     a = ap.parse_args()
     kw = {}
@@ -56,6 +57,9 @@ def main():
 
     for e in shards:
         e.reset()
+    if a.prefetch:
+        for i in range(S):
+            shards[i].set_prefetch_next(shards[(i + 1) % S], acts[(i + 1) % S])
     for t in range(200):
         step(t % S)
     torch.cuda.synchronize()
@@ -107,11 +111,13 @@ def main():
         wfin = np.stack([us_(3 + w) for w in range(4)], axis=1)
         nd = T[:, 10]
         print(f'--- trace {rep}: kernel span {end.max():.2f} us | CTA start spread {start.max():.2f} | ctr landed median {np.median(us_(12)):.2f} max {us_(12).max():.2f} | draws done median {np.median(drawn):.2f} max {drawn.max():.2f} | landed median {np.median(landed):.2f} '
-              f'max {landed.max():.2f} | warp step phase (from landed) median {np.median(wfin - landed[:, None]):.2f} '
-              f'p99 {np.percentile(wfin - landed[:, None], 99):.2f} max {(wfin - landed[:, None]).max():.2f} | '
+              f'max {landed.max():.2f} | warp step phase (from draws done) median {np.median(wfin - us_(13)[:, None]):.2f} '
+              f'p99 {np.percentile(wfin - us_(13)[:, None], 99):.2f} max {(wfin - us_(13)[:, None]).max():.2f} | '
               f'barrier1 median {np.median(b1):.2f} max {b1.max():.2f} | reset phase median {np.median((b2 - b1)[nd > 0]) if (nd > 0).any() else 0:.2f} '
               f'max {(b2 - b1).max():.2f} | tail (end - resets done) median {np.median(end - b2):.2f} max {(end - b2).max():.2f} | '
               f'end median {np.median(end):.2f}')
+        pc = lambda c: ' '.join(f'{np.percentile(us_(c), q):.2f}' for q in (0, 10, 50, 90, 100))
+        print(f'    percentiles 0/10/50/90/100 us: ctr {pc(12)} | draws part 0 {pc(11)} | tile landed {pc(2)} | hj issued + draws part 1 {pc(13)}')
         for kk in range(0, 7):
             sel = nd == kk
             if sel.any():
