@@ -1,0 +1,299 @@
+"""Batched on-device PPO around the B200 hover env (BASELINE.json configs[4]).
+
+Shape of ``IWPGAlgorithm.learn_one_epoch`` (algs/iwpg/iwpg.py:282-307) with the PPO clip loss of
+algs/ppo/ppo.py:22-40, re-hosted on the GPU: the rollout is ``T`` control steps of ``N`` envs per rank
+(``cf_step_dev``), advantages come from the fused GAE kernel (``cf_gae_dev``), and ranks average
+gradients / statistics over NCCL (``dist_utils``) where the reference uses MPI.  The two MLPs
+(34->50->50->4 relu, 34->64->64->1 tanh: 10 969 parameters) are library GEMMs through torch, not the
+product; ``state_dict`` keys equal the reference's (``pi.net.{0,2,4}``, ``pi.log_std``,
+``v.net.{0,2,4}``, ``obs_oms.*``, ``ret_oms.*``) so its ``torch_save/model*.pt`` checkpoints load.
+"""
+from __future__ import annotations
+
+import math
+import time
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import dist_utils as du
+
+
+class OnlineMeanStd(nn.Module):
+    """utils/online_mean_std.py:7-95: running mean / std with the parallel (Chan et al.) update; the
+    two MPI averages become two all-reduces over the ranks."""
+
+    def __init__(self, epsilon: float = 1e-5, shape=()):
+        super().__init__()
+        self.mean = nn.Parameter(torch.zeros(*shape), requires_grad=False)
+        self.std = nn.Parameter(torch.ones(*shape), requires_grad=False)
+        self.count = nn.Parameter(torch.zeros(1), requires_grad=False)
+        self.eps, self.bound, self.shape = epsilon, 10, shape
+
+    def forward(self, x: torch.Tensor, subtract_mean: bool = True, clip: bool = False) -> torch.Tensor:
+        y = (x - self.mean) / (self.std + self.eps) if subtract_mean else x / (self.std + self.eps)
+        return torch.clamp(y, -self.bound, self.bound) if clip else y
+
+    @torch.no_grad()
+    def update(self, x: torch.Tensor) -> None:
+        if self.shape[0] == 1:
+            x = x.reshape(-1, 1)
+        _, ws = du.world()
+        n_B = float(x.shape[0] * ws)
+        n_A = self.count.clone()
+        n_AB = self.count + n_B
+        batch_mean = du.mean_across_ranks(torch.mean(x, dim=0))
+        delta = batch_mean - self.mean
+        mean_new = self.mean + delta * n_B / n_AB
+        batch_var = du.mean_across_ranks(torch.mean((x - mean_new) ** 2, dim=0))
+        M2_AB = n_A * torch.square(self.std) + n_B * batch_var + delta ** 2 * (n_A * n_B / n_AB)
+        self.mean.data = mean_new
+        self.count.data = n_AB
+        self.std.data = torch.sqrt(M2_AB / n_AB)
+
+
+def _mlp(sizes, activation) -> nn.Sequential:
+    """build_mlp_network (algs/core.py:84-98): [Linear, act] per layer, Identity after the last;
+    kaiming_uniform weights (core.py:33-37)."""
+    layers = []
+    for j in range(len(sizes) - 1):
+        lin = nn.Linear(sizes[j], sizes[j + 1])
+        nn.init.kaiming_uniform_(lin.weight, a=math.sqrt(5))
+        layers += [lin, activation() if j < len(sizes) - 2 else nn.Identity()]
+    return nn.Sequential(*layers)
+
+
+class GaussianActor(nn.Module):
+    """MLPGaussianActor (algs/core.py:227-290)."""
+
+    def __init__(self, obs_dim: int, act_dim: int, hidden=(50, 50)):
+        super().__init__()
+        self.log_std = nn.Parameter(torch.full((act_dim,), math.log(0.5)), requires_grad=False)
+        self.net = _mlp([obs_dim] + list(hidden) + [act_dim], nn.ReLU)
+
+    def set_log_std(self, frac: float) -> None:                 # core.py:269-276
+        self.log_std.data.fill_(math.log(0.499 * frac + 0.01))
+
+    def log_prob(self, mu: torch.Tensor, act: torch.Tensor) -> torch.Tensor:
+        var = torch.exp(2.0 * self.log_std)
+        return (-((act - mu) ** 2) / (2.0 * var) - self.log_std - 0.5 * math.log(2.0 * math.pi)).sum(-1)
+
+    def entropy(self) -> torch.Tensor:
+        return (0.5 + 0.5 * math.log(2.0 * math.pi) + self.log_std).sum()
+
+
+class Critic(nn.Module):
+    """MLPCritic (algs/core.py:298-312)."""
+
+    def __init__(self, obs_dim: int, hidden=(64, 64)):
+        super().__init__()
+        self.net = _mlp([obs_dim] + list(hidden) + [1], nn.Tanh)
+
+    def forward(self, obs: torch.Tensor) -> torch.Tensor:
+        return self.net(obs).squeeze(-1)
+
+
+class ActorCritic(nn.Module):
+    """ActorCritic (algs/core.py:315-412) with the PPO defaults of algs/ppo/defaults.py:6-19."""
+
+    def __init__(self, obs_dim: int = 34, act_dim: int = 4, use_scaled_rewards: bool = True):
+        super().__init__()
+        self.obs_oms = OnlineMeanStd(shape=(obs_dim,))
+        self.pi = GaussianActor(obs_dim, act_dim)
+        self.v = Critic(obs_dim)
+        self.ret_oms = OnlineMeanStd(shape=(1,)) if use_scaled_rewards else None
+
+    @torch.no_grad()
+    def step(self, obs: torch.Tensor, deterministic: bool = False):
+        """(action, value, log_prob) for raw observations (core.py:371-394)."""
+        o = self.obs_oms(obs)
+        v = self.v(o)
+        mu = self.pi.net(o)
+        if deterministic:
+            return mu, v, torch.ones_like(v)
+        a = mu + torch.exp(self.pi.log_std) * torch.randn_like(mu)
+        return a, v, self.pi.log_prob(mu, a)
+
+    @torch.no_grad()
+    def value(self, obs: torch.Tensor) -> torch.Tensor:
+        return self.v(self.obs_oms(obs))
+
+
+class PPOTrainer:
+    """``ProximalPolicyOptimizationAlgorithm`` (algs/ppo/ppo.py) over a batched env.
+
+    One epoch = ``T`` control steps of the rank's ``N`` envs (``steps_per_epoch = T * N * world``), then
+    ``Buffer.finish_path`` for every path at once (fused GAE kernel), ``train_v_iterations`` x
+    ``num_mini_batches`` value updates, ``train_pi_iterations`` full-batch policy updates, running
+    statistics.  Hyper-parameter names and defaults follow iwpg.py:27-66 / ppo/defaults.py.
+    """
+
+    def __init__(self, env, rollout_len: int = 32, epochs: int = 300, gamma: float = 0.99, lam: float = 0.95,
+                 clip_ratio: float = 0.2, pi_lr: float = 3e-4, vf_lr: float = 1e-3, train_pi_iterations: int = 80,
+                 train_v_iterations: int = 5, num_mini_batches: int = 16, entropy_coef: float = 0.0,
+                 use_reward_scaling: bool = True, use_linear_lr_decay: bool = True,
+                 use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
+                 target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
+                 gae_fn=None):
+        if gae_fn is None:                                   # the fused CUDA kernel; tests of the host logic inject a stand-in
+            from .gae import gae as gae_fn
+        self._gae = gae_fn
+        self.env, self.T, self.N = env, int(rollout_len), env.num_envs
+        self.dev = env.device
+        self.rank, self.world = du.world()
+        self.epochs, self.gamma, self.lam, self.clip_ratio = epochs, gamma, lam, clip_ratio
+        self.train_pi_iterations, self.train_v_iterations = train_pi_iterations, train_v_iterations
+        self.num_mini_batches, self.entropy_coef = num_mini_batches, entropy_coef
+        self.use_reward_scaling, self.use_exploration_noise_anneal = use_reward_scaling, use_exploration_noise_anneal
+        self.use_kl_early_stopping, self.target_kl, self.check_freq = use_kl_early_stopping, target_kl, check_freq
+        self.pi_lr = pi_lr
+        torch.manual_seed(seed + 10000 * self.rank)             # iwpg.py:135-137: seed += 10000 * proc_id()
+        self.ac = (actor_critic or ActorCritic(env.obs_dim, 4, use_reward_scaling)).to(self.dev)
+        du.broadcast_params(list(self.ac.parameters()))          # mpi_tools.sync_params, iwpg.py:222
+        self.pi_optimizer = torch.optim.Adam(self.ac.pi.net.parameters(), lr=pi_lr)
+        self.vf_optimizer = torch.optim.Adam(self.ac.v.parameters(), lr=vf_lr)
+        self.scheduler = (torch.optim.lr_scheduler.LambdaLR(self.pi_optimizer, lambda e: 1 - e / self.epochs)
+                          if use_linear_lr_decay else None)
+        self._avg_pi = du.FlatGradAverager(list(self.ac.pi.net.parameters()))
+        self._avg_v = du.FlatGradAverager(list(self.ac.v.parameters()))
+        T, N, od = self.T, self.N, env.obs_dim
+        f = dict(dtype=torch.float32, device=self.dev)
+        self.obs_buf = torch.empty((T, N, od), **f)
+        self.act_buf = torch.empty((T, N, 4), **f)
+        self.rew_buf, self.val_buf, self.logp_buf = torch.empty((T, N), **f), torch.empty((T, N), **f), torch.empty((T, N), **f)
+        self.end_val_buf = torch.zeros((T, N), **f)
+        self.done_buf = torch.empty((T, N), dtype=torch.uint8, device=self.dev)
+        self.epoch = 0
+        self.total_env_steps = 0
+        self._obs = None
+        if getattr(env, '_term', None) is None:
+            raise ValueError('PPOTrainer needs make(..., return_terminal_obs=True): time-limit cuts bootstrap from V(s_T)')
+
+    # ------------------------------------------------------------------ rollout (iwpg.py:372-410)
+    @torch.no_grad()
+    def roll_out(self) -> None:
+        env, ac = self.env, self.ac
+        if self._obs is None:
+            self._obs = env.reset()
+        o = self._obs
+        for t in range(self.T):
+            a, v, logp = ac.step(o)
+            self.obs_buf[t].copy_(o)
+            self.act_buf[t].copy_(a)
+            self.val_buf[t].copy_(v)
+            self.logp_buf[t].copy_(logp)
+            o, r, d, info = env.step(a)                     # done envs are already reset: o holds their first obs
+            self.rew_buf[t].copy_(r)
+            self.done_buf[t].copy_(d)
+            # path end: v = 0 on a true terminal, V(s_T) on a time-limit cut (iwpg.py:392-397)
+            v_term = ac.value(info['terminal_observation'])
+            self.end_val_buf[t].copy_(torch.where(info['truncated'], v_term, torch.zeros_like(v_term)))
+        self._obs = o
+        self.last_val = ac.value(o)                         # epoch_ended: bootstrap the open paths (iwpg.py:391-394)
+        self.total_env_steps += self.T * self.N * self.world
+
+    # ------------------------------------------------------------------ update (iwpg.py:423-510)
+    def compute_loss_pi(self, obs, act, adv, logp_old):
+        mu = self.ac.pi.net(obs)
+        logp = self.ac.pi.log_prob(mu, act)
+        ratio = torch.exp(logp - logp_old)
+        clip_adv = adv * torch.clamp(ratio, 1 - self.clip_ratio, 1 + self.clip_ratio)
+        loss = -(torch.min(ratio * adv, clip_adv)).mean() - self.entropy_coef * self.ac.pi.entropy()
+        return loss, mu, ratio
+
+    def update(self) -> dict:
+        T, N = self.T, self.N
+        rew_scale = 0.0
+        if self.use_reward_scaling:                          # ret_oms(rews, subtract_mean=False, clip=True), core.py:519-527
+            rew_scale = 1.0 / (float(self.ac.ret_oms.std.item()) + self.ac.ret_oms.eps)
+        adv, target_v, disc_ret = self._gae(self.rew_buf, self.val_buf, self.done_buf, self.end_val_buf, self.last_val,
+                                            self.gamma, self.lam, rew_scale)
+        raw_obs = self.obs_buf.reshape(T * N, -1)
+        obs = self.ac.obs_oms(raw_obs).detach()              # pre_process_data, iwpg.py:350-370
+        act, adv = self.act_buf.reshape(T * N, 4), adv.reshape(T * N)
+        target_v, logp_old = target_v.reshape(T * N), self.logp_buf.reshape(T * N)
+        info = {}
+        # value net: train_v_iterations epochs of num_mini_batches shuffled mini-batches (iwpg.py:478-510)
+        B = T * N
+        mbs = B // self.num_mini_batches
+        with torch.no_grad():
+            info['loss_v_before'] = float(((self.ac.v(obs) - target_v) ** 2).mean())
+        for _ in range(self.train_v_iterations):
+            perm = torch.randperm(B, device=self.dev)
+            for start in range(0, mbs * self.num_mini_batches, mbs):
+                idx = perm[start:start + mbs]
+                self.vf_optimizer.zero_grad(set_to_none=False)
+                loss_v = ((self.ac.v(obs[idx]) - target_v[idx]) ** 2).mean()
+                loss_v.backward()
+                self._avg_v()                                # mpi_avg_grads(self.ac.v), iwpg.py:504
+                self.vf_optimizer.step()
+        # policy net: full-batch steps (iwpg.py:436-476)
+        with torch.no_grad():
+            mu_old = self.ac.pi.net(obs)
+        stop_iter = self.train_pi_iterations
+        for i in range(self.train_pi_iterations):
+            self.pi_optimizer.zero_grad(set_to_none=False)
+            loss_pi, mu, ratio = self.compute_loss_pi(obs, act, adv, logp_old)
+            if i == 0:
+                info['loss_pi_before'] = float(loss_pi)
+            loss_pi.backward()
+            self._avg_pi()                                   # mpi_avg_grads(self.ac.pi.net), iwpg.py:458
+            self.pi_optimizer.step()
+            if self.use_kl_early_stopping:
+                with torch.no_grad():                        # KL(N(mu_old, s) || N(mu_new, s)), same std
+                    kl = (((self.ac.pi.net(obs) - mu_old) ** 2) / (2.0 * torch.exp(2.0 * self.ac.pi.log_std))).sum(-1).mean()
+                if float(du.mean_across_ranks(kl.reshape(1))) > self.target_kl:
+                    stop_iter = i + 1
+                    break
+        info.update(loss_pi=float(loss_pi), stop_iter=stop_iter, policy_ratio=float(ratio.mean()))
+        # running statistics on the RAW data (iwpg.py:412-421)
+        self.ac.obs_oms.update(raw_obs)
+        if self.use_reward_scaling:
+            self.ac.ret_oms.update(disc_ret.reshape(-1))
+        return info
+
+    def _sync(self) -> None:
+        if self.dev.type == 'cuda':
+            torch.cuda.synchronize(self.dev)
+
+    # ------------------------------------------------------------------ epoch (iwpg.py:282-307)
+    def learn_one_epoch(self) -> dict:
+        t0 = time.time()
+        if self.use_exploration_noise_anneal:
+            self.ac.pi.set_log_std(1.0 - self.epoch / self.epochs)     # ac.update(frac), core.py:396-412
+        self.env.episode_stats(reset=True)
+        self.roll_out()
+        self._sync()
+        t1 = time.time()
+        info = self.update()
+        self._sync()
+        t2 = time.time()
+        st = self.env.episode_stats()
+        red = du.reduce_episode_stats(st['episodes'], st['return_sum'], st['length_sum'], float('inf'), float('-inf'), self.dev)
+        if self.scheduler is not None:
+            self.scheduler.step()
+        if self.epoch % self.check_freq == 0 and not du.check_distributed_parameters(self.ac):
+            raise RuntimeError('actor-critic parameters differ across ranks (iwpg.py:242-251)')
+        self.epoch += 1
+        info.update(epoch=self.epoch, EpRet=red['mean_return'], EpLen=red['mean_length'], episodes=red['episodes'],
+                    TotalEnvSteps=self.total_env_steps, rollout_s=t1 - t0, update_s=t2 - t1,
+                    FPS=self.T * self.N * self.world / (t2 - t0))
+        return info
+
+    def learn(self, epochs: Optional[int] = None, log=None):
+        for _ in range(epochs or self.epochs):
+            info = self.learn_one_epoch()
+            if log and self.rank == 0:
+                log(info)
+        return self.ac, self.env
+
+    # ------------------------------------------------------------------ checkpoints (loggers.py:371-446)
+    def save(self, path: str) -> None:
+        if self.rank == 0:
+            torch.save(self.ac.state_dict(), path)
+
+    def load(self, path: str) -> None:
+        sd = torch.load(path, map_location=self.dev)
+        self.ac.load_state_dict(sd, strict=False)
