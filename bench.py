@@ -53,6 +53,10 @@ def parse():
                          "shard's load/store phases overlap another's compute")
     ap.add_argument('--no-prefetch', action='store_true',
                     help='do not chain the shards with cf_set_prefetch_next (each step kernel asks the L2 to prefetch the next shard)')
+    ap.add_argument('--workload', default='hover_hj', choices=['hover_hj', 'initial', 'ppo'],
+                    help='hover_hj = BASELINE.json configs[2] (the headline); initial = configs[3] (DroneHoverBulletEnvWithAdversaryInitial-v0, '
+                         '131072 envs/GPU); ppo = configs[4] (rollout + fused GAE + PPO update, gradient all-reduce)')
+    ap.add_argument('--ground-effect', type=int, default=0, help='workload initial: use_ground_effect switch (reference: 0)')
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
@@ -105,13 +109,13 @@ def measured_peaks():
     return 6650.0, 'fallback 6.65 TB/s of B200_PROFILING.md (of fallback)'
 
 
-def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float):
+def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float, env_id: str = ENV_ID):
     """The reference algorithm on the host cores: oracle-B (float64 C restatement of the reference's
     Python + restated Bullet step, OpenMP over envs) on a bounded sample of the same workload."""
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import cf_oracle as co
     from disturbance_crazyfile_simulation_b200 import abi, hj_tables
-    cfg = abi.config_default(ENV_ID)
+    cfg = abi.config_default(env_id)
     V = hj_tables.synthetic_table(1.5, 15)
     for li in range(1, 21):          # one table shared by all levels: the lookup cost does not depend on its values
         co.set_table(li, V)
@@ -154,6 +158,12 @@ def main_reference(args):
     print(json.dumps(line))
 
 
+WORKLOADS = {
+    'hover_hj': dict(env_id='DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', envs=65536, tag='BASELINE.json configs[2]'),
+    'initial': dict(env_id='DroneHoverBulletEnvWithAdversaryInitial-v0', envs=131072, tag='BASELINE.json configs[3]'),
+}
+
+
 def main_ours(args):
     import torch
     import torch.distributed as dist
@@ -176,13 +186,19 @@ def main_ours(args):
         torch.cuda.synchronize()
 
     L = abi.lib()
+    wl = WORKLOADS[args.workload]
+    ENV_ID = wl['env_id']
+    if args.workload == 'initial':
+        args.envs = wl['envs'] if args.envs == 65536 else args.envs
+        args.shards = 4 if args.shards == 8 else args.shards
+    env_kw = {'use_ground_effect': args.ground_effect} if args.workload == 'initial' else {}
     n, S, K, W = args.envs, args.shards, args.steps, max(args.warmup, 3)
     shards = []
     for s in range(S):
         # global env ids: rank-major, then shard, so results do not depend on the number of GPUs;
         # one HJ table set per GPU, shared by its shards
         env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=(rank * S + s) * n,
-                   share_tables_with=shards[0] if shards else None)
+                   share_tables_with=shards[0] if shards else None, **env_kw)
         shards.append(env)
     od = shards[0].obs_dim
     g = torch.Generator(device=dev).manual_seed(1 + rank)
@@ -336,8 +352,8 @@ def main_ours(args):
             'metric': 'env-steps/sec (HJ-adversary hover)', 'value': value, 'unit': 'env-steps/s', 'n_gpus': world,
             'steps': K, 'warmup': W, 'ms_per_step': ms_max / K, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f'{ENV_ID}, {n} envs/GPU per step (BASELINE.json configs[2]); sensor noise, 10% domain '
-                                   'randomisation, Boltzmann HJ level, in-kernel auto-reset, TimeLimit 500 all on',
+            'config': {'workload': f'{ENV_ID}, {n} envs/GPU per step ({wl["tag"]}); sensor noise, 10% domain '
+                                   'randomisation, ' + ('Boltzmann HJ level' if args.workload == 'hover_hj' else f'HJ level 1.5, ground effect {args.ground_effect}') + ', in-kernel auto-reset, TimeLimit 500 all on',
                        'envs_per_gpu_per_step': n, 'shards_per_gpu': S,
                        'l2': f'inputs larger than L2: round-robin over {S} shards, {S * n * (304 + 16 + 4 * od + 9) / 1e6:.0f} MB '
                              'of state + I/O per GPU vs 126 MB L2', 'actions': 'hover + 0.05*N(0,1), resident in HBM',
@@ -362,7 +378,7 @@ def main_ours(args):
             'side': side,
         }
         if not args.no_cpu_baseline:
-            v, cores, steps_done, dt = cpu_reference_run(8192, 10000, 2, args.cpu_seconds)
+            v, cores, steps_done, dt = cpu_reference_run(8192, 10000, 2, args.cpu_seconds, ENV_ID)
             line['cpu_baseline'] = {'value': v, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port',
                                     'sample': f'8192 envs x {steps_done} control steps of the same workload ({dt:.1f} s), '
                                               'oracle-B float64 C restatement, OpenMP'}
@@ -373,9 +389,63 @@ def main_ours(args):
         dist.destroy_process_group()
 
 
+def main_ppo(args):
+    """BASELINE.json configs[4]: the PPO loop on DroneHoverBulletFreeEnvWithRandomHJAdversary-v0 - GPU rollout (policy MLP
+    + cf_step_dev), fused GAE (cf_gae_dev), value / policy updates with the gradient all-reduce over the ranks.
+    A "step" here is one epoch (T control steps of N envs per GPU + the update); value = env-steps/s end to end."""
+    import torch
+    import torch.distributed as dist
+    from disturbance_crazyfile_simulation_b200 import make
+    from disturbance_crazyfile_simulation_b200.trainer import PPOTrainer
+
+    world = int(os.environ.get('WORLD_SIZE', '1')); rank = int(os.environ.get('RANK', '0')); local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+    n, T = args.envs, 32
+    env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=rank * n, return_terminal_obs=True)
+    tr = PPOTrainer(env, rollout_len=T, epochs=300, seed=1)
+    K, W = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
+    for _ in range(W):
+        tr.learn_one_epoch()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    infos = [tr.learn_one_epoch() for _ in range(K)]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    if rank == 0:
+        roll = sum(i['rollout_s'] for i in infos) / K
+        upd = sum(i['update_s'] for i in infos) / K
+        print(json.dumps({
+            'metric': 'env-steps/sec (PPO end to end, HJ-adversary hover)', 'value': n * T * K * world / dt, 'unit': 'env-steps/s',
+            'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': 1e3 * dt / K, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'PPO on {ENV_ID} (BASELINE.json configs[4]): {n} envs/GPU x T={T} control steps per epoch, fused GAE, '
+                                   '5x16 value mini-batch steps + 80 full-batch policy steps (reference defaults), one flattened '
+                                   'gradient all-reduce per optimiser step', 'envs_per_gpu': n, 'rollout_len': T},
+            'side': {'rollout_s_per_epoch': roll, 'update_s_per_epoch': upd, 'rollout_env_steps_per_s': n * T * world / roll,
+                     'EpRet_last': infos[-1]['EpRet'], 'EpLen_last': infos[-1]['EpLen'], 'reference_logged_fps': '129-172 (BASELINE.md)'},
+            'gpu_launches': int(env.launch_count)}))
+    env.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == '__main__':
     a = parse()
     if a.impl == 'reference':
         main_reference(a)
+    elif a.workload == 'ppo':
+        main_ppo(a)
     else:
         main_ours(a)

@@ -237,7 +237,7 @@ class PPOTrainer:
             self.pi_optimizer.zero_grad(set_to_none=False)
             loss_pi, mu, ratio = self.compute_loss_pi(obs, act, adv, logp_old)
             if i == 0:
-                info['loss_pi_before'] = float(loss_pi)
+                info['loss_pi_before'] = float(loss_pi.detach())
             loss_pi.backward()
             self._avg_pi()                                   # mpi_avg_grads(self.ac.pi.net), iwpg.py:458
             self.pi_optimizer.step()
@@ -247,7 +247,7 @@ class PPOTrainer:
                 if float(du.mean_across_ranks(kl.reshape(1))) > self.target_kl:
                     stop_iter = i + 1
                     break
-        info.update(loss_pi=float(loss_pi), stop_iter=stop_iter, policy_ratio=float(ratio.mean()))
+        info.update(loss_pi=float(loss_pi.detach()), stop_iter=stop_iter, policy_ratio=float(ratio.detach().mean()))
         # running statistics on the RAW data (iwpg.py:412-421)
         self.ac.obs_oms.update(raw_obs)
         if self.use_reward_scaling:

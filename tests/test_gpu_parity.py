@@ -391,3 +391,57 @@ def test_gym_adapter_runs_reference_rollout_loop():
             o, ep_len, episodes = env.reset(), 0, episodes + 1
     assert episodes >= 2          # random actions crash quickly (episodic_data.csv: 20-110 steps)
     env.close()
+
+
+@pytest.mark.gpu
+def test_prefetch_hint_does_not_change_results():
+    """cf_set_prefetch_next is a hint: a chain of shards steps bit-identically with and without it."""
+    import torch
+    env_id, n = 'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', 1000      # partial last tile
+    def run(chain):
+        shards = []
+        for s in range(3):
+            shards.append(make(env_id, num_envs=n, seed=5, env_id_base=s * n, share_tables_with=shards[0] if shards else None))
+        acts = [torch.full((n, 4), 0.1 + 0.01 * s, device='cuda') for s in range(3)]
+        if chain:
+            for s in range(3):
+                shards[s].set_prefetch_next(shards[(s + 1) % 3], acts[(s + 1) % 3])
+        outs = [e.reset().clone() for e in shards]
+        for t in range(20):
+            for s in range(3):
+                o, r, d, _ = shards[s].step(acts[s])
+                outs.append(o.clone()); outs.append(r.clone())
+        st = [e.get_state() for e in shards]
+        if chain:
+            shards[0].set_prefetch_next(None)
+            shards[0].step(acts[0])
+        for e in shards:
+            e.close()
+        return outs, st
+    a, sa = run(False)
+    b, sb = run(True)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    assert all(np.array_equal(x.view(np.uint32), y.view(np.uint32)) for x, y in zip(sa, sb))
+
+
+@pytest.mark.gpu
+def test_ppo_trainer_epochs_gpu():
+    """configs[4] host loop on one GPU: rollout + fused GAE + updates run, statistics are finite, and the
+    GAE the trainer consumed equals the oracle's on the same buffers."""
+    import torch
+    from disturbance_crazyfile_simulation_b200.trainer import PPOTrainer
+    env = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=2048, seed=3, return_terminal_obs=True)
+    t = PPOTrainer(env, rollout_len=16, epochs=10, train_pi_iterations=4, train_v_iterations=2, num_mini_batches=4, seed=0)
+    for _ in range(2):
+        info = t.learn_one_epoch()
+        assert np.isfinite(info['loss_pi']) and np.isfinite(info['loss_v_before']) and info['episodes'] > 0
+        assert 1.0 <= info['EpLen'] <= 500.0 and info['EpRet'] < 0.0
+    assert float(t.ac.obs_oms.count) == 2 * 16 * 2048 and float(t.ac.ret_oms.std) > 0.0
+    scale = 1.0 / (float(t.ac.ret_oms.std) + 1e-5)
+    from disturbance_crazyfile_simulation_b200.gae import gae
+    adv, tgt, ret = gae(t.rew_buf, t.val_buf, t.done_buf, t.end_val_buf, t.last_val, 0.99, 0.95, scale)
+    ref = co.gae(t.rew_buf.cpu().numpy(), t.val_buf.cpu().numpy(), t.done_buf.cpu().numpy(), t.end_val_buf.cpu().numpy(),
+                 t.last_val.cpu().numpy(), 0.99, 0.95, scale)
+    for x, y in zip((adv, tgt, ret), ref):
+        assert np.allclose(x.cpu().numpy(), y, rtol=1e-5, atol=1e-3)
+    env.close()
