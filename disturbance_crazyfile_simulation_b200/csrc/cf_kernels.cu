@@ -290,6 +290,24 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (my_reset && t + 1 < k) p.load(g);
         }
         if (tr && tid == 0 && t == 0) tr[8] = gtimer();
+#ifndef CF_BULK_TAIL
+        // The tile's rows and state leave with 128-bit stores straight from shared memory (coalesced, conflict-free):
+        // unlike a bulk copy they do not have to be waited for, so the CTA's slot is free as soon as they are issued.
+        if (bulk_obs) {
+            float4* dst = reinterpret_cast<float4*>(io.obs + ((size_t)t * n + (size_t)tile * CF_TILE) * OD);
+            const float4* src = reinterpret_cast<const float4*>(s_obs);
+#pragma unroll
+            for (int j = tid; j < CF_TILE * OD / 4; j += CF_TILE) dst[j] = src[j];
+        } else if (valid) {
+            copy_row<OD>(io.obs + r * OD, row);
+        }
+        if (t + 1 == k) {
+            float4* dst = reinterpret_cast<float4*>(gtile);
+            const float4* src = reinterpret_cast<const float4*>(s_state);
+#pragma unroll
+            for (int j = tid; j < CF_DYN_WORDS * CF_TILE / 4; j += CF_TILE) dst[j] = src[j];
+        }
+#else
         if (bulk_obs) {
             if (tid == 0) {
                 bulk_s2g(io.obs + ((size_t)t * n + (size_t)tile * CF_TILE) * OD, s_obs, kObsBytes);
@@ -305,6 +323,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                 bulk_wait_read();
             }
         }
+#endif
         if (t + 1 < k) __syncthreads();                     // rows may be overwritten by the next step's draws
     }
     if (tr && tid == 0) { tr[9] = gtimer(); tr[10] = (unsigned long long)total_done; }
