@@ -79,6 +79,8 @@ _SIGS = {
     'cf_step_k_dev': (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, _P, _P]),
     'cf_reset_host': (C.c_int, [_P, _P, _P]),
     'cf_step_host': (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P]),
+    'cf_step_host_async': (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P]),
+    'cf_host_sync': (C.c_int, [_P]),
     'cf_get_state': (C.c_int, [_P, _P]),
     'cf_set_state': (C.c_int, [_P, _P]),
     'cf_get_levels': (C.c_int, [_P, _P]),

@@ -481,8 +481,8 @@ int cf_reset_host(cf_env* e, const uint8_t* mask, float* obs) {
     return CF_OK;
 }
 
-int cf_step_host(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
-                 uint8_t* truncated) {
+static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
+                             uint8_t* truncated, bool wait) {
     if (!e || !act || !obs || !rew || !done) return fail(CF_ERR_INVALID, "cf_step: null argument%s", "");
     CU(cudaSetDevice(e->device));
     const size_t n = e->n, od = e->obs_dim;
@@ -507,7 +507,22 @@ int cf_step_host(cf_env* e, const float* act, float* obs, float* rew, uint8_t* d
     if (cost) CU(cudaMemcpyAsync(cost, e->d_cost, n * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (term_obs) CU(cudaMemcpyAsync(term_obs, e->d_term, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (truncated) CU(cudaMemcpyAsync(truncated, e->d_trunc, n, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    if (wait) CU(cudaStreamSynchronize(st));
+    return CF_OK;
+}
+
+int cf_step_host(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
+                 uint8_t* truncated) {
+    return step_host_enqueue(e, act, obs, rew, done, cost, term_obs, truncated, true);
+}
+int cf_step_host_async(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
+                       uint8_t* truncated) {
+    return step_host_enqueue(e, act, obs, rew, done, cost, term_obs, truncated, false);
+}
+int cf_host_sync(cf_env* e) {
+    if (!e) return fail(CF_ERR_INVALID, "cf_host_sync: null handle%s", "");
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->hstream));
     return CF_OK;
 }
 

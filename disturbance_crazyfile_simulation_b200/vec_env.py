@@ -269,6 +269,14 @@ class CrazyFlieVecEnv:
         p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
         abi.check(self._L.cf_step_host(self._h, p(act), p(obs), p(rew), p(done), p(cost), p(term_obs), p(truncated)))
 
+    def step_host_async(self, act, obs, rew, done, cost=None, term_obs=None, truncated=None):
+        """step_host without the wait: pinned buffers stay untouched until :meth:`host_sync` returns."""
+        p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        abi.check(self._L.cf_step_host_async(self._h, p(act), p(obs), p(rew), p(done), p(cost), p(term_obs), p(truncated)))
+
+    def host_sync(self):
+        abi.check(self._L.cf_host_sync(self._h))
+
     def close(self):
         if getattr(self, '_h', None) is not None and self._h.value:
             self._L.cf_destroy(self._h)

@@ -177,6 +177,13 @@ int cf_reset_host(cf_env* env, const uint8_t* mask, float* obs);
 int cf_step_host(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
                  float* cost, float* term_obs, uint8_t* truncated);
 
+/* The same step, not waited for: the copies and the kernel are queued on the handle's private stream and the call
+ * returns; the host buffers (pinned: cf_host_alloc) must stay untouched until cf_host_sync(env) returns.  Lets a caller
+ * with several handles overlap one handle's download with the next one's upload and kernel. */
+int cf_step_host_async(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
+                       float* cost, float* term_obs, uint8_t* truncated);
+int cf_host_sync(cf_env* env);
+
 /* ---- state / parity hooks ----------------------------------------------------------- */
 int cf_get_state(cf_env* env, float* state_host /* [n][CF_STATE_WORDS] */);
 int cf_set_state(cf_env* env, const float* state_host);

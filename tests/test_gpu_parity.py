@@ -445,3 +445,22 @@ def test_ppo_trainer_epochs_gpu():
     for x, y in zip((adv, tgt, ret), ref):
         assert np.allclose(x.cpu().numpy(), y, rtol=1e-5, atol=1e-3)
     env.close()
+
+
+@pytest.mark.gpu
+def test_host_async_matches_host_sync():
+    """cf_step_host_async + cf_host_sync give the results of cf_step_host (pipelined callers)."""
+    env_id, n = 'DroneHoverBulletFreeEnvWithAdversary-v0', 300
+    a, b = make(env_id, num_envs=n, seed=9), make(env_id, num_envs=n, seed=9)
+    od = a.obs_dim
+    mk = lambda: (np.zeros((n, od), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros(n, np.float32))
+    oa, ra, da, ca = mk(); ob, rb, db, cb = mk()
+    a.reset_host(oa); b.reset_host(ob)
+    assert np.array_equal(oa, ob)
+    act = np.full((n, 4), 0.12, np.float32)
+    for t in range(10):
+        a.step_host(act, oa, ra, da, ca)
+        b.step_host_async(act, ob, rb, db, cb)
+        b.host_sync()
+        assert np.array_equal(oa, ob) and np.array_equal(ra, rb) and np.array_equal(da, db) and np.array_equal(ca, cb)
+    a.close(); b.close()

@@ -58,8 +58,10 @@ def main():
     for e in shards:
         e.reset()
     if a.prefetch:
+        ns0 = a.streams[0]
         for i in range(S):
-            shards[i].set_prefetch_next(shards[(i + 1) % S], acts[(i + 1) % S])
+            nxt = i + ns0 if i + ns0 < S else i % ns0       # the shard this shard's stream steps next (first --streams value)
+            shards[i].set_prefetch_next(shards[nxt], acts[nxt])
     for t in range(200):
         step(t % S)
     torch.cuda.synchronize()
@@ -74,10 +76,10 @@ def main():
                 st.wait_stream(main)
             for j in range(S * gr):
                 i = j % S
-                if j % ns == 0:
+                if i % ns == 0:                              # a shard always steps on the same stream
                     step(i)
                 else:
-                    with torch.cuda.stream(side[j % ns - 1]):
+                    with torch.cuda.stream(side[i % ns - 1]):
                         step(i)
             for st in side:
                 main.wait_stream(st)
