@@ -120,6 +120,7 @@ def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float, env_id
     V = hj_tables.synthetic_table(1.5, 15)
     for li in range(1, 21):          # one table shared by all levels: the lookup cost does not depend on its values
         co.set_table(li, V)
+    co.lib().cfo_set_num_threads(os.cpu_count() or 1)        # all host cores, whatever OMP_NUM_THREADS the launcher exported
     orc = co.OracleEnvs(cfg, envs, seed=1)
     orc.reset()
     rng = np.random.default_rng(0)

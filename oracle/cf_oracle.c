@@ -713,6 +713,14 @@ void cfo_step_batch(cfo_env* envs, int n, const cf_config* cfg, const double* ac
         if (truncated) truncated[i] = (uint8_t)tr;
     }
 }
+/* bench.py's CPU baseline uses every host core even when the launcher (torchrun) exported OMP_NUM_THREADS=1 */
+void cfo_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
 int cfo_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();
