@@ -58,6 +58,10 @@ def parse():
                     help='hover_hj = BASELINE.json configs[2] (the headline); initial = configs[3] (DroneHoverBulletEnvWithAdversaryInitial-v0, '
                          '131072 envs/GPU); ppo = configs[4] (rollout + fused GAE + PPO update, gradient all-reduce)')
     ap.add_argument('--ground-effect', type=int, default=0, help='workload initial: use_ground_effect switch (reference: 0)')
+    ap.add_argument('--actions', default='hover_noise', choices=['hover_noise', 'uniform', 'pd'],
+                    help='action source (SURVEY 8d config 3): hover + 0.05 N(0,1) resident in HBM (headline); U(-1,1) resident in HBM '
+                         '(short episodes, reset-heavy); pd = on-device attitude-rate PD on the noisy obs, one extra kernel per step '
+                         '(episodes run to the 500-step limit)')
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
@@ -204,7 +208,12 @@ def main_ours(args):
         shards.append(env)
     od = shards[0].obs_dim
     g = torch.Generator(device=dev).manual_seed(1 + rank)
-    acts = [(HOVER + 0.05 * torch.randn((n, 4), device=dev, generator=g)).contiguous() for _ in range(S)]
+    if args.actions == 'uniform':
+        acts = [(2.0 * torch.rand((n, 4), device=dev, generator=g) - 1.0).contiguous() for _ in range(S)]
+    else:
+        acts = [(HOVER + 0.05 * torch.randn((n, 4), device=dev, generator=g)).contiguous() for _ in range(S)]
+    PD = args.actions == 'pd'
+    pd_gains = (C.c_float * 6)(HOVER, 0.5, 0.3, 8.0, 0.05, 0.05)
     obs = [torch.empty((n, od), device=dev) for _ in range(S)]
     rew = [torch.empty(n, device=dev) for _ in range(S)]
     done = [torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(S)]
@@ -220,6 +229,8 @@ def main_ours(args):
         rc = L.cf_step_dev(shards[i]._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, stream)
         if rc:
             abi.check(rc)
+        if PD:                                           # the next action of this shard from the observation just written
+            abi.check(L.cf_pd_actions_dev(P(obs[i]), od, n, P(acts[i]), pd_gains, stream))
 
     for e in shards:
         e.reset()
@@ -282,7 +293,7 @@ def main_ours(args):
     barrier()
     t1 = time.time()
     ms = ev0.elapsed_time(ev1)
-    launches = K                                         # one k_step launch per control step (graph nodes included)
+    launches = K * (2 if PD else 1)                      # one k_step launch per control step (graph nodes included) [+ k_pd_actions]
     clocks = sampler.stop(t0, t1) if sampler else None
     kern_ms = ms / K                                     # launch-to-launch time of the dominant kernel inside the timed region
     t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -372,7 +383,8 @@ def main_ours(args):
                                    'randomisation, ' + ('Boltzmann HJ level' if args.workload == 'hover_hj' else f'HJ level 1.5, ground effect {args.ground_effect}') + ', in-kernel auto-reset, TimeLimit 500 all on',
                        'envs_per_gpu_per_step': n, 'shards_per_gpu': S,
                        'l2': f'inputs larger than L2: round-robin over {S} shards, {S * n * (304 + 16 + 4 * od + 9) / 1e6:.0f} MB '
-                             'of state + I/O per GPU vs 126 MB L2', 'actions': 'hover + 0.05*N(0,1), resident in HBM',
+                             'of state + I/O per GPU vs 126 MB L2', 'actions': {'hover_noise': 'hover + 0.05*N(0,1), resident in HBM', 'uniform': 'U(-1,1), resident in HBM',
+                                   'pd': 'on-device attitude-rate PD on the noisy observation (cf_pd_actions_dev, one extra kernel per step)'}[args.actions],
                        'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
                                     'packed 2-bit sign tables in HBM/L2',
                        'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S * GP} ({GP} passes over the {S} shards)')

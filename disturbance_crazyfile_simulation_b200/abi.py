@@ -93,6 +93,7 @@ _SIGS = {
     'cf_set_prefetch_next': (C.c_int, [_P, _P, _P]),
     'cf_set_trace_buffer': (C.c_int, [_P, _P]),
     'cf_num_tiles': (C.c_int, [_P]),
+    'cf_pd_actions_dev': (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P]),
     'cf_launch_count': (C.c_int64, [_P]),
     'cf_kernel_timing': (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'cf_host_alloc': (_P, [C.c_uint64]),

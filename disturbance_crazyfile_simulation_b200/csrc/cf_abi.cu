@@ -635,6 +635,15 @@ int cf_gae_dev(const float* rew, const float* val, const uint8_t* done, const fl
     return CF_OK;
 }
 
+int cf_pd_actions_dev(const float* obs, int32_t obs_dim, int32_t n, float* act, const float gains[6], void* stream) {
+    if (!obs || !act || !gains || n < 1 || (obs_dim != 34 && obs_dim != 42) || ((uintptr_t)act & 15))
+        return fail(CF_ERR_INVALID, "cf_pd_actions: bad argument%s", "");
+    const PdGains g{gains[0], gains[1], gains[2], gains[3], gains[4], gains[5]};
+    launch_pd_actions(obs, obs_dim, obs_dim == 34 ? 17 : 21, n, act, g, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
 int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int32_t T, int32_t N, float* adv, float* target_v,
                 float* disc_ret) {

@@ -34,9 +34,12 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
 // ---------------------------------------------------------------------------------- RNG
 // Philox4x32-10, counter = (gid_lo, event counter, block, tag ^ gid_hi<<8), key = seed.  The ten
 // round keys are derived on the host (DevCfg::pk) so they are constant-bank operands here.
+#ifndef CF_PHILOX_ROUNDS
+#define CF_PHILOX_ROUNDS 10             /* tools/ only: instruction-count sensitivity probes build with fewer rounds */
+#endif
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, const DevCfg& cfg) {
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < CF_PHILOX_ROUNDS; ++r) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
         uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
         c = make_uint4(hi1 ^ c.y ^ cfg.pk[r][0], lo1, hi0 ^ c.w ^ cfg.pk[r][1], lo0);
@@ -306,27 +309,61 @@ __device__ __forceinline__ int hj_signbits(const DevTables& tab, int level_idx, 
 // of the level's table at the nearest grid cell of (rpy, body rates).  Split in two so that the gather is in
 // flight while the motor model runs: `issue` returns the raw table byte (packed mode) or the decoded bits
 // (value-table mode) plus the shift, `hj_bits` extracts the two bits where the torque is needed.
-struct HjFetch { uint32_t raw; int shift; };
+// Packed mode fetches the aligned 32-bit word that holds the cell's two bits with an asynchronous copy into a
+// per-thread shared-memory slot (cp.async, SASS LDGSTS): no register scoreboard is tied up while it is in flight,
+// so nothing issued between `issue` and `hj_bits` (the second half of the step's draws, the motor model) can
+// end up waiting for the gather by scoreboard aliasing.
+struct HjFetch { uint32_t raw; int shift; uint32_t* slot; };
+__device__ __forceinline__ void cp_async_4(uint32_t* dst_smem, const void* src_gmem) {
+#ifdef CF_GATHER_EVICT_LAST
+    // the few MB of table cells the envs actually visit should outlive the ~46 MB of state and I/O streamed per step
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;"
+                 ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem), "l"(pol) : "memory");
+#else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem) : "memory");
+#endif
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
 template <int HJ_MODE>
 __device__ __forceinline__ HjFetch hj_disturbance_issue(const float q[4], const float wb[3], const DevCfg& cfg,
-                                                        const DevTables& tab, const float* thr, int level_idx) {
+                                                        const DevTables& tab, const float* thr, int level_idx, uint32_t* slot) {
     float rpy[3];
     quat2euler_hj(q, rpy);
     int idx[6];
 #pragma unroll
     for (int k = 0; k < 3; ++k) { idx[k] = hj_index_f32(rpy[k], k, thr, cfg); idx[3 + k] = hj_index_f32(wb[k], 3 + k, thr, cfg); }
     HjFetch f;
+    f.slot = nullptr;
     if (HJ_MODE == CF_HJ_SIGN_TABLE) {
         const int c = hj_cell(idx);
-        f.raw = __ldg(tab.signs + (size_t)level_idx * CF_SIGN_STRIDE + (c >> 2));
-        f.shift = 2 * (c & 3);
+        const uint8_t* base = tab.signs + (size_t)level_idx * CF_SIGN_STRIDE;      // slab and stride are 256-byte multiples
+        if (slot) {
+#ifdef CF_PROBE_NOGATHER
+            *slot = (uint32_t)c;                               // tools/ only: the step without the table gather's latency
+#else
+            cp_async_4(slot, base + 4 * (c >> 4));
+#endif
+            f.raw = 0u; f.slot = slot; f.shift = 2 * (c & 15);
+        } else {
+            f.raw = __ldg(base + (c >> 2));
+            f.shift = 2 * (c & 3);
+        }
     } else {
         f.raw = (uint32_t)hj_signbits_value(tab.value[level_idx], idx);
         f.shift = 0;
     }
     return f;
 }
-__device__ __forceinline__ int hj_bits(const HjFetch& f) { return (int)((f.raw >> f.shift) & 3u); }
+__device__ __forceinline__ int hj_bits(const HjFetch& f) {
+    uint32_t raw = f.raw;
+    if (f.slot) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        raw = *reinterpret_cast<volatile uint32_t*>(f.slot);
+    }
+    return (int)((raw >> f.shift) & 3u);
+}
 
 // ---------------------------------------------------------------------------------- sensors
 // SensorNoise.add_noise_to_omega (envs/sensors.py:121-134) at dt = 1/SIM_FREQ, followed by
@@ -765,15 +802,16 @@ __device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCf
 
 // The HJ table fetch of a step, issued from the tile as soon as it has landed (step_env consumes it).
 template <int HJ_MODE>
-__device__ __forceinline__ HjFetch step_issue_hj(const EnvRef e, const DevCfg& cfg, const DevTables& tab, const float* thr) {
+__device__ __forceinline__ HjFetch step_issue_hj(const EnvRef e, const DevCfg& cfg, const DevTables& tab, const float* thr,
+                                                 uint32_t* slot) {
     HjFetch f;
-    f.raw = 0u; f.shift = 0;
+    f.raw = 0u; f.shift = 0; f.slot = nullptr;
     const int level = misc_level(e.u(CF_S_MISC));
     if ((cfg.dstb_kind == CF_DSTB_HJ_FIXED || cfg.dstb_kind == CF_DSTB_HJ_BOLTZMANN) && level > 0) {
         float q[4], ow[3], R[9], wb[3];
         e.get4(CF_S_QUAT, q); e.get3(CF_S_OMEGA_W, ow);
         quat_to_R(q, R); matTvec(R, ow, wb);
-        f = hj_disturbance_issue<HJ_MODE>(q, wb, cfg, tab, thr, level);
+        f = hj_disturbance_issue<HJ_MODE>(q, wb, cfg, tab, thr, level, slot);
     }
     return f;
 }

@@ -33,8 +33,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // global -> shared, completion counted in bytes on the mbarrier (16-byte aligned, 16-byte multiple)
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+#ifdef CF_STREAM_EVICT_FIRST
+    uint64_t pol;                                           // the tile is read once per step: first in line for eviction
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+#else
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+#endif
 }
 // shared -> global, tracked by the thread's bulk async-group
 __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
@@ -119,6 +126,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     uint64_t* mbar = reinterpret_cast<uint64_t*>(s_ctx + RC * 32);
     int* s_ndone = reinterpret_cast<int*>(mbar + 1);        // [2]
     uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
+    uint32_t* s_hj = reinterpret_cast<uint32_t*>(s_list + CF_TILE);   // [CF_TILE] landing slots of the sign-table gather (cp.async)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x, i = tile * CF_TILE + tid;
     float* gtile = S + (size_t)tile * (CF_STATE_WORDS * CF_TILE);
     const bool valid = i < n;
@@ -127,7 +135,11 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     unsigned long long* tr = io.trace ? io.trace + CF_TRACE_WORDS * (size_t)tile : nullptr;    // per-CTA timeline (debug)
     if (tr && tid == 0) { tr[0] = smid(); tr[1] = gtimer(); }
     // the event counter first (the draws wait for it), then the tile: it should not queue behind 15 MB of bulk copies
+#ifdef CF_PROBE_NOCTR
+    const uint32_t ctr0 = 7u + (uint32_t)k;                 // tools/ only: how much of a CTA's life is the wait for its counter word
+#else
     const uint32_t ctr0 = __float_as_uint(__ldcg(gtile + CF_S_RNG_CTR * CF_TILE + tid));
+#endif
     if (tid == 0) {
         s_ndone[0] = 0;
         mbar_init(mbar, 1);
@@ -154,17 +166,17 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     if (tr && tid == 0) {
         asm volatile("" :: "r"(ctr0)); tr[12] = gtimer();
     }
-    __syncthreads();                                        // mbarrier initialised, thresholds in place
     DrawSrc dw0 = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
     if (valid) pregen_step_draws<NOISE, 0>(dw0, cfg, scratch, sd);   // step event of the launch's first step: counter ctr0, tag 0
     if (tr && tid == 0) tr[11] = gtimer();
+    __syncthreads();                                        // mbarrier initialised, thresholds in place (first needed from here on)
     mbar_wait(mbar, 0);
     if (tr && tid == 0) tr[2] = gtimer();
     HjFetch hjf;
-    hjf.raw = 0u; hjf.shift = 0;
+    hjf.raw = 0u; hjf.shift = 0; hjf.slot = nullptr;
     if (valid) {
         consume_fresh(e, cfg, gid, NOISE);
-        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr);   // the table gather is in flight behind the second half of the draws
+        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, s_hj + tid);   // the table gather is in flight behind the second half of the draws
         pregen_step_draws<NOISE, 1>(dw0, cfg, scratch, sd);
     }
     if (tr && tid == 0) tr[13] = gtimer();
@@ -176,7 +188,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (t > 0) {
                 av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
                 const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr);
+                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, s_hj + tid);
                 pregen_step_draws<NOISE, 0>(dw, cfg, scratch, sd);
                 pregen_step_draws<NOISE, 1>(dw, cfg, scratch, sd);
             }
@@ -236,6 +248,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         reset_task_stale(EnvRef{s_state + s_list[c0 + j]}, *c);
                     }
                     __syncthreads();
+                    if (tr && tid == 0 && t == 0 && c0 == 0) tr[14] = gtimer();
                     // R2, one env per lane: pose + motor state (warp 0) | domain randomisation, counters, level (warp 1) |
                     // gyro-free part of the first (warp 2) and second (warp 3) observation + action history
                     if (lane < cnt) {
@@ -254,6 +267,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         }
                     }
                     __syncthreads();
+                    if (tr && tid == 0 && t == 0 && c0 == 0) tr[15] = gtimer();
                     // R3: the gyro samples of both observations (need the new body rate and the old gyro state)
                     if (warp == 0 && lane < cnt) {
                         const int et = s_list[c0 + lane];
@@ -419,6 +433,28 @@ __global__ void k_gae(const float* __restrict__ rew, const float* __restrict__ v
     }
 }
 
+// Synthetic "PID actions" source of the throughput runs (BASELINE.json north_star: "random/PID actions"): an
+// attitude -> rate -> motor-mix PD law on the env's own NOISY observation, one thread per env.  Structure after
+// the firmware cascade the reference cites (envs/control.py:13-26 gains table, :33-50 rpy_control_factors_to_PWM,
+// QUAD_FORMATION_X mixing; :94-100 PWM = 30000 + 30000 a), expressed in action units; gains are arguments.
+// obs rows [n][obs_dim], o(k) = (pos3, quat xyzw, vel3, gyro3) at float offset `off`.
+__global__ void k_pd_actions(const float* __restrict__ obs, int obs_dim, int off, int n, float* __restrict__ act, PdGains g) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* o = obs + (size_t)i * obs_dim + off;
+    const float z = o[2], qx = o[3], qy = o[4], qz = o[5], qw = o[6], vz = o[9], wx = o[10], wy = o[11], wz = o[12];
+    const float roll = atan2f(2.0f * (qw * qx + qy * qz), 1.0f - 2.0f * (qx * qx + qy * qy));
+    const float pitch = asinf(clampf(2.0f * (qw * qy - qz * qx), -1.0f, 1.0f));
+    const float T = g.hover + g.kz * (1.0f - z) - g.kvz * vz;
+    const float r = g.krate * (-g.katt * roll - wx), p = g.krate * (-g.katt * pitch - wy), y = g.kyaw * (-wz);
+    float4 a;
+    a.x = clampf(T - r - p - y, -1.0f, 1.0f);
+    a.y = clampf(T - r + p + y, -1.0f, 1.0f);
+    a.z = clampf(T + r + p - y, -1.0f, 1.0f);
+    a.w = clampf(T + r - p + y, -1.0f, 1.0f);
+    reinterpret_cast<float4*>(act)[i] = a;
+}
+
 // ---------------------------------------------------------------------------------- launchers
 static inline int blocks_for(int n, int threads) { return (n + threads - 1) / threads; }
 
@@ -441,7 +477,7 @@ void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float
 
 size_t step_smem_bytes(int obs_dim) {
     const int rc = CF_TILE >= 128 ? 4 : 2;
-    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + rc * 96 * 4 + rc * 32 * 4 + 8 + 8 + CF_TILE;
+    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + rc * 96 * 4 + rc * 32 * 4 + 8 + 8 + CF_TILE + CF_TILE * 4;
 }
 
 template <bool NOISE, int HJ_MODE>
@@ -495,6 +531,9 @@ void launch_gae(const float* rew, const float* val, const uint8_t* done, const f
                 cudaStream_t st) {
     k_gae<<<blocks_for(N, 128), 128, 0, st>>>(rew, val, done, end_val, last_val, gamma, lam, rew_scale, T, N, adv, tgt,
                                               disc_ret);
+}
+void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st) {
+    k_pd_actions<<<blocks_for(n, 128), 128, 0, st>>>(obs, obs_dim, off, n, act, g);
 }
 
 }  // namespace cf

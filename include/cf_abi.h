@@ -225,6 +225,13 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
  * (nullable, [n]) receive the return and length of each env's LAST finished episode. */
 int cf_episode_stats(cf_env* env, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host);
 
+/* ---- synthetic "PID actions" source of the throughput runs ------------------------------------
+ * Attitude -> rate -> motor-mix PD law on the NOISY observation rows (device pointers, asynchronous): structure of
+ * the firmware cascade the reference cites (envs/control.py:13-26 gains, :33-50 rpy_control_factors_to_PWM,
+ * :94-100 PWM.act), in action units.  obs [n][obs_dim] (34 or 42), act [n][4] 16-byte aligned,
+ * gains = {hover action, kz, kvz, k_attitude [1/s], k_rate [action per rad/s], k_yaw_rate}. */
+int cf_pd_actions_dev(const float* obs, int32_t obs_dim, int32_t n, float* act, const float gains[6], void* stream);
+
 /* ---- pinned host memory for the host-pointer API (so its copies are asynchronous DMA) ------- */
 void* cf_host_alloc(uint64_t bytes);     /* NULL on failure (cf_last_error) */
 void cf_host_free(void* p);
@@ -238,8 +245,10 @@ int cf_kernel_timing(cf_env* env, int32_t enable, int32_t reset, double* avg_ms,
 /* Tracing hook: when `trace_dev` (DEVICE pointer, [cf_num_tiles][16] uint64, caller-owned, zeroed by the caller)
  * is set, every step launch records per tile (times in %globaltimer ns): [0] SM id, [1] CTA start, [2] state tile
  * landed in shared memory, [3..6] warp 0..3 finished the step phase, [7] tile barrier passed, [8] in-place resets
- * done, [9] CTA end, [10] envs of the tile that finished an episode.  NULL switches tracing off (the default;
- * no cost beyond a predicate). */
+ * done, [9] CTA end, [10] envs of the tile that finished an episode, [11] first half of the step's draws generated,
+ * [12] event counter arrived, [13] table gather issued + second half of the draws generated, [14] / [15] reset
+ * draws ready / reset tasks done (first group of finished envs).  NULL switches tracing off (the default; no cost
+ * beyond a predicate). */
 int cf_set_trace_buffer(cf_env* env, uint64_t* trace_dev);
 int cf_num_tiles(const cf_env* env);     /* tiles of envs the step kernel launches (one CTA each) */
 

@@ -464,3 +464,95 @@ def test_host_async_matches_host_sync():
         b.host_sync()
         assert np.array_equal(oa, ob) and np.array_equal(ra, rb) and np.array_equal(da, db) and np.array_equal(ca, cb)
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+def test_pd_actions_kernel_and_closed_loop():
+    """cf_pd_actions_dev against its formula in NumPy, and closed loop: with the PD law on the noisy observation the
+    RandomHJ hover env reaches its 500-step TimeLimit in most episodes (the CPU oracle gives a mean length of ~486)."""
+    import torch
+    from disturbance_crazyfile_simulation_b200.pd_actions import DEFAULT_GAINS, pd_actions
+    env = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=4096, seed=11)
+    obs = env.reset()
+    act = pd_actions(obs)
+    o = obs.cpu().numpy()[:, 17:30].astype(np.float64)
+    h, kz, kvz, ka, kr, ky = [np.float64(np.float32(v)) for v in DEFAULT_GAINS]
+    roll = np.arctan2(2 * (o[:, 6] * o[:, 3] + o[:, 4] * o[:, 5]), 1 - 2 * (o[:, 3] ** 2 + o[:, 4] ** 2))
+    pitch = np.arcsin(np.clip(2 * (o[:, 6] * o[:, 4] - o[:, 5] * o[:, 3]), -1, 1))
+    T = h + kz * (1 - o[:, 2]) - kvz * o[:, 9]
+    r, p, y = kr * (-ka * roll - o[:, 10]), kr * (-ka * pitch - o[:, 11]), ky * (-o[:, 12])
+    want = np.clip(np.stack([T - r - p - y, T - r + p + y, T + r + p - y, T + r - p + y], 1), -1, 1)
+    assert np.abs(act.cpu().numpy() - want).max() < 2e-6
+    for _ in range(600):
+        obs, rew, done, info = env.step(act)
+        pd_actions(obs, act)
+    stats = env.episode_stats()
+    assert stats['episodes'] > 4096 and stats['mean_length'] > 350.0, stats
+
+
+@pytest.mark.gpu
+def test_full_size_properties_65536():
+    """BASELINE.json configs[2] at its full size (65 536 envs, RandomHJ, noise + DR + auto-reset on), checked through
+    size-independent properties: bit-identical results when the envs are sharded 2 x 32 768 (RNG keyed by the global
+    env id), the Boltzmann level histogram (envs/utils.py:27-39, p ~ exp(-level)), unit quaternions, domain-randomised
+    parameters inside +-10 %, episode lengths <= 500, and done flags that agree with compute_done evaluated in
+    float64 on the post-step states of a no-auto-reset twin."""
+    import torch
+    env_id, n = 'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', 65536
+    full = make(env_id, num_envs=n, seed=5)
+    lo = make(env_id, num_envs=n // 2, seed=5, env_id_base=0, share_tables_with=full)
+    hi = make(env_id, num_envs=n // 2, seed=5, env_id_base=n // 2, share_tables_with=full)
+    o = full.reset().clone()
+    assert torch.equal(o, torch.cat([lo.reset(), hi.reset()]))
+    g = torch.Generator(device='cuda').manual_seed(3)
+    hover = 2.0 / 1.8 - 1.0
+    ndone = 0
+    for t in range(60):
+        act = (hover + 0.3 * torch.randn((n, 4), device='cuda', generator=g)).contiguous()
+        a, ra, da, ia = full.step(act)
+        b = torch.cat([lo.step(act[: n // 2])[0], hi.step(act[n // 2:])[0]])
+        assert torch.equal(a, b), f'step {t}: sharded result differs'
+        assert bool(torch.isfinite(a).all()) and bool(torch.isfinite(ra).all())
+        ndone += int(da.sum())
+    assert ndone > 1000                                       # the in-kernel auto-reset path ran many times
+    st = co.state_record_from_f32(full.get_state())
+    F = abi.STATE_FIELDS
+    q = st[:, F['quat'][0]:F['quat'][0] + 4]
+    assert np.abs(np.linalg.norm(q, axis=1) - 1.0).max() < 1e-5
+    assert st[:, F['ep_len'][0]].max() <= 500
+    for name, nom in (('mass', 0.030), ('dt', 0.005), ('ftf1', 5.96e-3)):
+        v = st[:, F[name][0]]
+        assert v.min() >= nom * 0.9 * (1 - 1e-6) and v.max() <= nom * 1.1 * (1 + 1e-6), name
+    # Boltzmann level histogram of the running episodes (level drawn at the end of every reset)
+    lv = (st[:, F['misc'][0]].astype(np.int64) % 256)
+    p = np.exp(-np.arange(21) / 10.0); p /= p.sum()
+    cnt = np.bincount(lv, minlength=21)[:21]
+    assert cnt.sum() == n
+    z = (cnt - n * p) / np.sqrt(n * p * (1 - p))
+    assert np.abs(z).max() < 5.0, z
+    # done flags against compute_done (hover_free.py:449-461) in float64 on the true post-step state
+    twin = make(env_id, num_envs=n, seed=5, auto_reset=0, share_tables_with=full)
+    twin.reset()
+    mism = 0
+    for t in range(25):
+        act = (hover + 0.3 * torch.randn((n, 4), device='cuda', generator=g)).contiguous()
+        _, _, d, _ = twin.step(act)
+        s = co.state_record_from_f32(twin.get_state())
+        qq, pos, ow = s[:, 4:8], s[:, 0:3], s[:, 11:14]
+        x, y, zq, w = qq.T
+        roll = np.arctan2(2 * (w * x + y * zq), 1 - 2 * (x * x + y * y))
+        pitch = np.arcsin(np.clip(2 * (w * y - zq * x), -1, 1))
+        R = np.stack([1 - 2 * (y * y + zq * zq), 2 * (x * y - w * zq), 2 * (x * zq + w * y),
+                      2 * (x * y + w * zq), 1 - 2 * (x * x + zq * zq), 2 * (y * zq - w * x),
+                      2 * (x * zq - w * y), 2 * (y * zq + w * x), 1 - 2 * (x * x + y * y)], 1).reshape(-1, 3, 3)
+        wb = np.einsum('nji,nj->ni', R, ow)
+        want = (pos[:, 2] < 0.2) | (np.abs(roll) > np.deg2rad(75)) | (np.abs(pitch) > np.deg2rad(75)) | \
+               (np.rad2deg(np.abs(wb)) > 1000).any(1) | (s[:, F['ep_len'][0]] >= 500)
+        got = d.cpu().numpy().astype(bool)
+        # a threshold met within float32 resolution may legitimately differ from its float64 re-evaluation
+        margin = np.minimum.reduce([np.abs(pos[:, 2] - 0.2), np.abs(np.abs(roll) - np.deg2rad(75)),
+                                    np.abs(np.abs(pitch) - np.deg2rad(75)), np.abs(np.rad2deg(np.abs(wb)) - 1000).min(1) / 1000])
+        mism += int(((want != got) & (margin > 1e-5)).sum())
+    assert mism == 0
+    for e in (full, lo, hi, twin):
+        e.close()

@@ -120,6 +120,10 @@ def main():
               f'end median {np.median(end):.2f}')
         pc = lambda c: ' '.join(f'{np.percentile(us_(c), q):.2f}' for q in (0, 10, 50, 90, 100))
         print(f'    percentiles 0/10/50/90/100 us: ctr {pc(12)} | draws part 0 {pc(11)} | tile landed {pc(2)} | hj issued + draws part 1 {pc(13)}')
+        if (nd > 0).any():
+            r1, r2 = us_(14)[nd > 0], us_(15)[nd > 0]
+            print(f'    reset sub-phases (tiles with resets, first group): R1 draws {np.median(r1 - b1[nd > 0]):.2f} | R2 tasks {np.median(r2 - r1):.2f} | '
+                  f'R3 gyro + rest {np.median(b2[nd > 0] - r2):.2f} us')
         for kk in range(0, 7):
             sel = nd == kk
             if sel.any():
