@@ -494,7 +494,7 @@ def test_pd_actions_kernel_and_closed_loop():
 def test_full_size_properties_65536():
     """BASELINE.json configs[2] at its full size (65 536 envs, RandomHJ, noise + DR + auto-reset on), checked through
     size-independent properties: bit-identical results when the envs are sharded 2 x 32 768 (RNG keyed by the global
-    env id), the Boltzmann level histogram (envs/utils.py:27-39, p ~ exp(-level)), unit quaternions, domain-randomised
+    env id), the Boltzmann level histogram after a reset (envs/utils.py:27-39, p ~ exp(-level)), unit quaternions, domain-randomised
     parameters inside +-10 %, episode lengths <= 500, and done flags that agree with compute_done evaluated in
     float64 on the post-step states of a no-auto-reset twin."""
     import torch
@@ -523,16 +523,17 @@ def test_full_size_properties_65536():
     for name, nom in (('mass', 0.030), ('dt', 0.005), ('ftf1', 5.96e-3)):
         v = st[:, F[name][0]]
         assert v.min() >= nom * 0.9 * (1 - 1e-6) and v.max() <= nom * 1.1 * (1 + 1e-6), name
-    # Boltzmann level histogram of the running episodes (level drawn at the end of every reset)
-    lv = (st[:, F['misc'][0]].astype(np.int64) % 256)
+    # done flags against compute_done (hover_free.py:449-461) in float64 on the true post-step state
+    twin = make(env_id, num_envs=n, seed=5, auto_reset=0, share_tables_with=full)
+    twin.reset()
+    # Boltzmann level histogram right after a reset of all envs (later snapshots are length-biased: episodes at
+    # different levels last differently long)
+    lv = (co.state_record_from_f32(twin.get_state())[:, F['misc'][0]].astype(np.int64) % 256)
     p = np.exp(-np.arange(21) / 10.0); p /= p.sum()
     cnt = np.bincount(lv, minlength=21)[:21]
     assert cnt.sum() == n
     z = (cnt - n * p) / np.sqrt(n * p * (1 - p))
     assert np.abs(z).max() < 5.0, z
-    # done flags against compute_done (hover_free.py:449-461) in float64 on the true post-step state
-    twin = make(env_id, num_envs=n, seed=5, auto_reset=0, share_tables_with=full)
-    twin.reset()
     mism = 0
     for t in range(25):
         act = (hover + 0.3 * torch.randn((n, 4), device='cuda', generator=g)).contiguous()
