@@ -136,7 +136,10 @@ class PPOTrainer:
                  use_reward_scaling: bool = True, use_linear_lr_decay: bool = True,
                  use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
                  target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
-                 gae_fn=None):
+                 gae_fn=None, logger=None, save_freq: int = 10):
+        # logger: a run_logger.RunLogger (progress.csv / config.json / torch_save/model{epoch}.pt in the reference's
+        # formats, loggers.py:205-513); save_freq as iwpg.py:45,302-304
+        self.logger, self.save_freq, self.seed, self._t_start = logger, int(save_freq), seed, time.time()
         if gae_fn is None:                                   # the fused CUDA kernel; tests of the host logic inject a stand-in
             from .gae import gae as gae_fn
         self._gae = gae_fn
@@ -170,6 +173,16 @@ class PPOTrainer:
         self._obs = None
         if getattr(env, '_term', None) is None:
             raise ValueError('PPOTrainer needs make(..., return_terminal_obs=True): time-limit cuts bootstrap from V(s_T)')
+        if self.logger is not None:                          # logger.save_config(self.params), iwpg.py:126
+            self.logger.save_config(dict(alg='ppo', env_id=getattr(env, 'id', None), num_envs=self.N, world_size=self.world,
+                                         rollout_len=self.T, epochs=epochs, gamma=gamma, lam=lam, clip_ratio=clip_ratio,
+                                         pi_lr=pi_lr, vf_lr=vf_lr, train_pi_iterations=train_pi_iterations,
+                                         train_v_iterations=train_v_iterations, num_mini_batches=num_mini_batches,
+                                         entropy_coef=entropy_coef, use_reward_scaling=use_reward_scaling,
+                                         use_linear_lr_decay=use_linear_lr_decay,
+                                         use_exploration_noise_anneal=use_exploration_noise_anneal,
+                                         use_kl_early_stopping=use_kl_early_stopping, target_kl=target_kl, seed=seed,
+                                         save_freq=save_freq))
 
     # ------------------------------------------------------------------ rollout (iwpg.py:372-410)
     @torch.no_grad()
@@ -272,6 +285,7 @@ class PPOTrainer:
         t2 = time.time()
         st = self.env.episode_stats()
         red = du.reduce_episode_stats(st['episodes'], st['return_sum'], st['length_sum'], float('inf'), float('-inf'), self.dev)
+        current_lr = self.scheduler.get_last_lr()[0] if self.scheduler is not None else self.pi_lr
         if self.scheduler is not None:
             self.scheduler.step()
         if self.epoch % self.check_freq == 0 and not du.check_distributed_parameters(self.ac):
@@ -280,7 +294,36 @@ class PPOTrainer:
         info.update(epoch=self.epoch, EpRet=red['mean_return'], EpLen=red['mean_length'], episodes=red['episodes'],
                     TotalEnvSteps=self.total_env_steps, rollout_s=t1 - t0, update_s=t2 - t1,
                     FPS=self.T * self.N * self.world / (t2 - t0))
+        if self.logger is not None:
+            self._log_epoch(info, current_lr)
         return info
+
+    def _log_epoch(self, info: dict, current_lr: float) -> None:
+        """One progress.csv row with the column names of IWPGAlgorithm.log (iwpg.py:309-348) for the quantities the
+        batched trainer tracks, then the periodic checkpoint (iwpg.py:302-304).  Episode statistics are the means the
+        step kernel accumulates on the device; per-episode rows (episodic_data.csv) are left to gym-style callers."""
+        lg = self.logger
+        lg.log_tabular('Epoch', info['epoch'])
+        lg.log_tabular('EpRet/Mean', float(info['EpRet']))
+        lg.log_tabular('EpLen/Mean', float(info['EpLen']))
+        lg.log_tabular('Loss/Pi', info['loss_pi_before'])
+        lg.log_tabular('Loss/Value', info['loss_v_before'])
+        lg.log_tabular('Loss/DeltaPi', info['loss_pi'] - info['loss_pi_before'])
+        lg.log_tabular('Misc/StopIter', info['stop_iter'])
+        lg.log_tabular('Misc/Seed', self.seed)
+        lg.log_tabular('PolicyRatio', info['policy_ratio'])
+        lg.log_tabular('LR', current_lr)
+        if self.use_reward_scaling:
+            lg.log_tabular('Misc/RewScaleMean', float(self.ac.ret_oms.mean.item()))
+            lg.log_tabular('Misc/RewScaleStddev', float(self.ac.ret_oms.std.item()))
+        if self.use_exploration_noise_anneal:
+            lg.log_tabular('Misc/ExplorationNoiseStd', float(torch.exp(self.ac.pi.log_std[0]).item()))
+        lg.log_tabular('TotalEnvSteps', info['TotalEnvSteps'])
+        lg.log_tabular('Time', int(time.time() - self._t_start))
+        lg.log_tabular('FPS', int(info['FPS']))
+        lg.dump_tabular()
+        if self.epoch % self.save_freq == 0 or self.epoch == self.epochs:
+            lg.torch_save(self.ac.state_dict(), itr=self.epoch)
 
     def learn(self, epochs: Optional[int] = None, log=None):
         for _ in range(epochs or self.epochs):

@@ -135,8 +135,11 @@ def _gae_cpu(rew, val, done, end_val, last_val, gamma, lam, rew_scale):
 def _trainer(rank, world):
     base, cnt = du.shard_range(64, rank, world)
     env = _FakeEnv(cnt, base)
+    import tempfile
+    from disturbance_crazyfile_simulation_b200.run_logger import RunLogger
+    log_dir = tempfile.mkdtemp()
     t = tr.PPOTrainer(env, rollout_len=8, epochs=4, train_pi_iterations=3, train_v_iterations=2, num_mini_batches=4,
-                      seed=3, gae_fn=_gae_cpu, check_freq=1)
+                      seed=3, gae_fn=_gae_cpu, check_freq=1, logger=RunLogger(log_dir, rank=rank), save_freq=2)
     w0 = torch.cat([p.detach().reshape(-1).clone() for p in t.ac.pi.net.parameters()])
     for _ in range(2):
         info = t.learn_one_epoch()                          # raises if the ranks' parameters diverge
@@ -148,6 +151,17 @@ def _trainer(rank, world):
     gathered = [torch.zeros_like(w1) for _ in range(world)]
     dist.all_gather(gathered, w1)
     assert torch.equal(gathered[0], gathered[1])
+    # run directory: only rank 0 writes; two epochs -> header + 2 rows, config.json, model2.pt
+    import os
+    if rank == 0:
+        rows = open(os.path.join(log_dir, 'progress.csv')).read().strip().split('\n')
+        assert len(rows) == 3 and rows[0].startswith('Epoch,EpRet/Mean,EpLen/Mean,Loss/Pi,Loss/Value')
+        assert rows[2].split(',')[0] == '2' and rows[0].split(',')[-3:] == ['TotalEnvSteps', 'Time', 'FPS']
+        assert os.path.exists(os.path.join(log_dir, 'config.json'))
+        sd = torch.load(os.path.join(log_dir, 'torch_save', 'model2.pt'))
+        assert 'pi.net.0.weight' in sd and 'obs_oms.mean' in sd
+    else:
+        assert os.listdir(log_dir) == []
 
 
 def test_trainer_epoch_world2():
