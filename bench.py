@@ -32,8 +32,11 @@ HOVER = 2.0 / 1.8 - 1.0
 # 216 B out, DR params 56 B in, action 16 B in, obs 136 B + reward 4 B + done 1 B + cost 4 B out,
 # HJ packed sign table 1 B gathered.
 BYTES_PER_ENV_STEP = 216 + 216 + 56 + 16 + 136 + 4 + 1 + 4 + 1
-# dram__bytes_read.sum + dram__bytes_write.sum per k_step launch, from the committed ncu capture (None until measured)
-TRAFFIC_NCU = None
+# dram__bytes_read.sum + dram__bytes_write.sum per k_step launch (bytes), mean of the 3 launches of the committed
+# ncu --set full capture profiles/r1_v5_ncu_summary.md (caches flushed per replay): 42.36 MB read (this shard's state +
+# actions + parameters, and the next shard's 21 MB prefetched into L2) + 0.05 MB written during the kernel; the
+# ~25 MB of new state and I/O rows stay dirty in the 126 MB L2 and are written back while later launches run.
+TRAFFIC_NCU = 42.41e6
 
 
 def parse():
