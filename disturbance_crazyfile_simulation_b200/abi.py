@@ -93,6 +93,13 @@ _SIGS = {
     'cf_set_prefetch_next': (C.c_int, [_P, _P, _P]),
     'cf_set_trace_buffer': (C.c_int, [_P, _P]),
     'cf_num_tiles': (C.c_int, [_P]),
+    'cf_hj_solver_create': (C.c_int, [_P, C.c_int32, _P]),
+    'cf_hj_solver_destroy': (C.c_int, [_P]),
+    'cf_hj_solver_set_value': (C.c_int, [_P, _P]),
+    'cf_hj_solver_get_value': (C.c_int, [_P, _P]),
+    'cf_hj_solver_update': (C.c_int, [_P, C.c_float, C.c_float, _P, _P]),
+    'cf_hj_solver_run': (C.c_int, [_P, C.c_double, C.c_double, C.c_int64, _P, _P]),
+    'cf_hj_solver_timing': (C.c_int, [_P, _P, _P]),
     'cf_pd_actions_dev': (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P]),
     'cf_launch_count': (C.c_int64, [_P]),
     'cf_kernel_timing': (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),

@@ -30,6 +30,13 @@ int cuda_fail(cudaError_t e, const char* where) {
         if (e_ != cudaSuccess) return cuda_fail(e_, #call);       \
     } while (0)
 
+}  // namespace
+namespace cf {
+// error text for entry points implemented in other translation units (cf_hj_solver.cu)
+void set_error(const char* where, const char* what) { snprintf(g_err, sizeof(g_err), "%s: %s", where, what); }
+}  // namespace cf
+namespace {
+
 constexpr double kPiD = 3.141592653589793;
 double deg2rad(double x) { return kPiD * x / 180.0; }
 

@@ -21,6 +21,7 @@ void launch_levels(const float* S, int n, float* out, cudaStream_t st);
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int T, int N, float* adv, float* tgt, float* disc_ret,
                 cudaStream_t st);
+void set_error(const char* where, const char* what);     // cf_abi.cu: text behind cf_last_error()
 struct PdGains { float hover, kz, kvz, katt, krate, kyaw; };
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st);
 

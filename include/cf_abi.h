@@ -232,6 +232,38 @@ int cf_episode_stats(cf_env* env, int32_t reset, double out[4], float* fin_ret_h
  * gains = {hover action, kz, kvz, k_attitude [1/s], k_rate [action per rad/s], k_yaw_rate}. */
 int cf_pd_actions_dev(const float* obs, int32_t obs_dim, int32_t n, float* act, const float gains[6], void* stream);
 
+/* ---- HJ value-table generator ---------------------------------------------------------
+ * The FasTrack solve that produces fastrack_{level}_15x15.npy in the reference
+ * (adversarial_generation/FasTrack_data/Fastrack.py:281-320 -> odp/solver.py:83-233 -> odp/computeGraphs/graph_6D.py
+ * with odp/spatialDerivatives/first_orderENO6D.py, accuracy "low", TargetSetMode maxVWithV0), float32 like the
+ * reference's HeteroCL build.  All scalars arrive rounded to float32 by the caller; sin / cos of the grid values of
+ * dims 0, 1 are tabulated by the caller.  Value arrays are C-order [pts]^6 floats. */
+#define CF_HJ_MAX_PTS 16
+typedef struct cf_hj_problem {
+    int32_t pts;                        /* grid points per dimension, 3..CF_HJ_MAX_PTS */
+    int32_t reserved;
+    float x[6][CF_HJ_MAX_PTS];          /* grid values (odp Grid.vs, GridProcessing.py:6-51) */
+    float sin_phi[CF_HJ_MAX_PTS], cos_phi[CF_HJ_MAX_PTS], tan_theta[CF_HJ_MAX_PTS], cos_theta[CF_HJ_MAX_PTS];
+    double target_sq[6][CF_HJ_MAX_PTS]; /* float64 (x_d - center_d)^2 per dim, 0 for ignored dims: l0 = (float)sum (Fastrack.py:296-306) */
+    float dx[6];
+    float u_min[3], u_max[3], d_min[3], d_max[3];   /* Fastrack.py:22-23, 42-44 */
+    float c[3], inertia[3];                         /* (Iyy-Izz)/Ixx, (Izz-Ixx)/Iyy, (Ixx-Iyy)/Izz; Ixx, Iyy, Izz */
+} cf_hj_problem;
+typedef struct cf_hj_solver cf_hj_solver;
+/* V starts at l0 (solver.py:108) */
+int cf_hj_solver_create(const cf_hj_problem* prob, int32_t device, cf_hj_solver** out);
+int cf_hj_solver_destroy(cf_hj_solver* s);
+int cf_hj_solver_set_value(cf_hj_solver* s, const float* V_host);
+int cf_hj_solver_get_value(cf_hj_solver* s, float* V_host);
+/* one call of the compiled graph_6D kernel with t = (t0, t1): V <- max(V + rate * dt, l0); returns the advanced
+ * t0 and, when info != NULL, {min_deriv[6], max_deriv[6], max_alpha[6], dt} (graph_6D.py:64-330) */
+int cf_hj_solver_update(cf_hj_solver* s, float t0, float t1, float* t0_new, float info[19]);
+/* the time loop of HJSolver (solver.py:152-206) over tau = arange(0, lookback + 1e-5, t_step); max_updates <= 0: no cap */
+int cf_hj_solver_run(cf_hj_solver* s, double lookback, double t_step, int64_t max_updates, int64_t* updates_done,
+                     double* t_final);
+/* average device time of one update (all its kernels) over the updates run so far, in ms */
+int cf_hj_solver_timing(cf_hj_solver* s, double* avg_ms_per_update, int64_t* updates);
+
 /* ---- pinned host memory for the host-pointer API (so its copies are asynchronous DMA) ------- */
 void* cf_host_alloc(uint64_t bytes);     /* NULL on failure (cf_last_error) */
 void cf_host_free(void* p);
