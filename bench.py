@@ -337,6 +337,24 @@ def main_ours(args):
     del g_rew, g_val, g_done, g_last
     stats = e0.episode_stats()
     side['mean_episode_length_shard0'] = stats['mean_length']
+    # (d) HJ value-table generator: full-size (15^6) updates of the FasTrack solve, rank 0 only.
+    # Algorithmic bytes per update: V read once + V' written once (l0 is recomputed, the stencil's neighbour reads are
+    # cache hits by design) = 2 * 4 * 15^6 = 91.1 MB.
+    if rank == 0:
+        from disturbance_crazyfile_simulation_b200 import hj_solver
+        hs = hj_solver.HjSolver(hj_solver.fastrack_problem(1.5, 15), device=local)
+        hs.run(2.0, 1e-3, max_updates=20)
+        ms0, n0 = hs.timing()
+        hs.run(2.0, 1e-3, max_updates=200)
+        ms1, n1 = hs.timing()
+        upd_ms = (ms1 * n1 - ms0 * n0) / max(1, n1 - n0)
+        side['hj_solver'] = {'grid': '15^6', 'ms_per_update': upd_ms, 'cells_per_s': 15 ** 6 / (upd_ms * 1e-3),
+                             'bytes_per_update': 2 * 4 * 15 ** 6, 'achieved_gb_s': 2 * 4 * 15 ** 6 / (upd_ms * 1e-3) / 1e9,
+                             'updates_timed': n1 - n0,
+                             'note': 'float32, bit-identical to the NumPy restatement of optimized_dp graph_6D (accuracy low); '
+                                     'latency / instruction bound (13-point 6-D stencil, IEEE divisions kept for exactness), '
+                                     'not HBM bound'}
+        hs.close()
 
     # ---- e2e: the public host-pointer API (cf_step_host) with pinned HOST buffers ---------------
     def pinned(shape, dtype):
