@@ -55,6 +55,15 @@ def main():
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         abi.check(L.cf_step_dev(shards[i]._h, P(acts[i]), P(obs[i]), P(rew[i]), P(done[i]), P(cost[i]), None, None, st))
 
+    if kw.get('rng_mode') == abi.CF_RNG_INJECTED:
+        # PROBE ONLY: the step kernel with its draws read from buffers instead of generated (what a separate
+        # generator kernel would feed it); the same random buffers every step, so this is not a valid simulation
+        r = np.random.default_rng(0)
+        for e in shards:
+            e.set_noise_override(step_z=r.standard_normal((abi.CF_STEP_NORMALS, n)).astype(np.float32),
+                                 step_u=r.random((abi.CF_STEP_UNIFORMS, n), dtype=np.float32),
+                                 reset_z=r.standard_normal((abi.CF_RESET_NORMALS, n)).astype(np.float32),
+                                 reset_u=r.random((abi.CF_RESET_UNIFORMS, n), dtype=np.float32))
     for e in shards:
         e.reset()
     if a.prefetch:
