@@ -29,6 +29,9 @@
 namespace {
 
 __constant__ cf_hj_problem c_p;
+// ((0 + sq0[i]) + sq1[j]) + sq2[k] of the target sum in float64, pre-added on the host in the reference's order
+// (Fastrack.py:296-306): the per-cell sum continues with dims 3, 4, 5
+__constant__ double c_sq012[CF_HJ_MAX_PTS * CF_HJ_MAX_PTS * CF_HJ_MAX_PTS];
 
 // global scalars of an update, in device memory
 struct HjGlobals {
@@ -65,22 +68,6 @@ __device__ __forceinline__ void coords(unsigned c, int idx[6]) {
     for (int d = 5; d >= 0; --d) { idx[d] = (int)(c % pts); c /= pts; }
 }
 
-// first_orderENO6D.py, the same rule in every dimension
-__device__ __forceinline__ void one_sided(const float* __restrict__ V, unsigned c, int i, unsigned stride, int pts, float dx, float vc,
-                                          float& L, float& R) {
-    if (i == 0) {
-        float vn = __ldg(V + c + stride);
-        float lb = add(vc, mul(fabsf(sub(vn, vc)), sgn(vc)));
-        L = dvd(sub(vc, lb), dx); R = dvd(sub(vn, vc), dx);
-    } else if (i == pts - 1) {
-        float vp = __ldg(V + c - stride);
-        float rb = add(vc, mul(fabsf(sub(vc, vp)), sgn(vc)));
-        L = dvd(sub(vc, vp), dx); R = dvd(sub(rb, vc), dx);
-    } else {
-        L = dvd(sub(vc, __ldg(V + c - stride)), dx); R = dvd(sub(__ldg(V + c + stride), vc), dx);
-    }
-}
-
 // UAV6D.dynamics (Fastrack.py:133-167) at grid cell idx: f[0..2] (no torque enters) and the torque-free part
 // base[i] = (c_i x) y of f[3 + i]; f[3 + i] = base[i] + (u_i + d_i) / I_i
 __device__ __forceinline__ void dynamics_parts(const int idx[6], float f[3], float base[3]) {
@@ -92,6 +79,33 @@ __device__ __forceinline__ void dynamics_parts(const int idx[6], float f[3], flo
     base[0] = mul(mul(c_p.c[0], r), q);
     base[1] = mul(mul(c_p.c[1], p), r);
     base[2] = mul(mul(c_p.c[2], p), q);
+}
+// The per-cell table lookups (grid values, trig, target squares) indexed by l, m, n differ from lane to lane, which the
+// constant cache serialises: k_update stages them in shared memory once per CTA.
+struct CellTab {
+    float x3[CF_HJ_MAX_PTS], x4[CF_HJ_MAX_PTS], x5[CF_HJ_MAX_PTS];
+    float sphi[CF_HJ_MAX_PTS], cphi[CF_HJ_MAX_PTS], tth[CF_HJ_MAX_PTS], cth[CF_HJ_MAX_PTS];
+    double sq3[CF_HJ_MAX_PTS], sq4[CF_HJ_MAX_PTS], sq5[CF_HJ_MAX_PTS];
+    float c[3];
+};
+__device__ __forceinline__ void fill_tab(CellTab& t) {
+    const int i = threadIdx.x;
+    if (i < CF_HJ_MAX_PTS) {
+        t.x3[i] = c_p.x[3][i]; t.x4[i] = c_p.x[4][i]; t.x5[i] = c_p.x[5][i];
+        t.sphi[i] = c_p.sin_phi[i]; t.cphi[i] = c_p.cos_phi[i]; t.tth[i] = c_p.tan_theta[i]; t.cth[i] = c_p.cos_theta[i];
+        t.sq3[i] = c_p.target_sq[3][i]; t.sq4[i] = c_p.target_sq[4][i]; t.sq5[i] = c_p.target_sq[5][i];
+        if (i < 3) t.c[i] = c_p.c[i];
+    }
+}
+__device__ __forceinline__ void dynamics_parts(const CellTab& t, const int idx[6], float f[3], float base[3]) {
+    const float sphi = t.sphi[idx[0]], cphi = t.cphi[idx[0]], tth = t.tth[idx[1]], cth = t.cth[idx[1]];
+    const float p = t.x3[idx[3]], q = t.x4[idx[4]], r = t.x5[idx[5]];
+    f[0] = add(add(p, mul(mul(r, cphi), tth)), mul(mul(q, sphi), tth));
+    f[1] = sub(mul(q, cphi), mul(r, sphi));
+    f[2] = add(dvd(mul(r, cphi), cth), dvd(mul(q, sphi), cth));
+    base[0] = mul(mul(t.c[0], r), q);
+    base[1] = mul(mul(t.c[1], p), r);
+    base[2] = mul(mul(t.c[2], p), q);
 }
 // max over the 4 (u, d) corner combinations of |base + (u + d) / I| (graph_6D.py:232-290), same order of maxima
 __device__ __forceinline__ float corner_alpha(float base, const float (*tq)[3], int i) {
@@ -129,15 +143,30 @@ __device__ __forceinline__ void block_minmax12(float v[12], float* out) {
     }
 }
 
-// derivatives of one cell: L[d], R[d] (graph_6D.py:89-101 with accuracy "low")
+// derivatives of one cell: L[d], R[d] (graph_6D.py:89-101 with accuracy "low").  All 12 neighbour loads are issued
+// before the first use (clamped addresses at the ends: the value loaded there is never selected), and the three
+// cases of first_orderENO6D.py are selects over the same numerators, so there is no branch and no serialised wait.
 template <int PTS>
 __device__ __forceinline__ void cell_derivs(const float* __restrict__ V, unsigned c, const int idx[6], float vc, float L[6], float R[6]) {
     const int pts = npts<PTS>();
+    float vm[6], vp[6];
     unsigned stride = 1;
 #pragma unroll
     for (int d = 5; d >= 0; --d) {
-        one_sided(V, c, idx[d], stride, pts, c_p.dx[d], vc, L[d], R[d]);
+        vp[d] = __ldg(V + c + (idx[d] < pts - 1 ? stride : 0u));
+        vm[d] = __ldg(V + c - (idx[d] > 0 ? stride : 0u));
         stride *= (unsigned)pts;
+    }
+    const float sg = sgn(vc);
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+        const float dn = sub(vp[d], vc), dp = sub(vc, vm[d]);               // forward / backward difference
+        const float lb = add(vc, mul(fabsf(dn), sg));                       // left_boundary  (used at index 0)
+        const float rb = add(vc, mul(fabsf(dp), sg));                       // right_boundary (used at index pts-1)
+        const float numL = idx[d] == 0 ? sub(vc, lb) : dp;
+        const float numR = idx[d] == pts - 1 ? sub(rb, vc) : dn;
+        L[d] = dvd(numL, c_p.dx[d]);
+        R[d] = dvd(numR, c_p.dx[d]);
     }
 }
 
@@ -286,9 +315,9 @@ __global__ void __launch_bounds__(kThreads) k_choose(const float* __restrict__ p
 template <int PTS>
 __device__ __forceinline__ float target_l0(const int idx[6]) {
     // l0 = FasTrackTarget: float64 sum of the per-dimension squares, rounded once (Fastrack.py:296-306)
-    double t = 0.0;
+    double t = c_sq012[(idx[0] * CF_HJ_MAX_PTS + idx[1]) * CF_HJ_MAX_PTS + idx[2]];
 #pragma unroll
-    for (int d = 0; d < 6; ++d) t = __dadd_rn(t, c_p.target_sq[d][idx[d]]);
+    for (int d = 3; d < 6; ++d) t = __dadd_rn(t, c_p.target_sq[d][idx[d]]);
     return (float)t;
 }
 
@@ -298,6 +327,8 @@ __global__ void __launch_bounds__(kThreads, CF_HJ_UPDATE_MIN_BLOCKS) k_update(co
                                                      const HjGlobals* __restrict__ g) {
     __shared__ float tq[4][3], hq[3][3];
     __shared__ float dt_s;
+    __shared__ CellTab tab;
+    fill_tab(tab);
     if (threadIdx.x < 12) tq[threadIdx.x / 3][threadIdx.x % 3] = g->tq[threadIdx.x / 3][threadIdx.x % 3];
     else if (threadIdx.x < 21) hq[(threadIdx.x - 12) / 3][(threadIdx.x - 12) % 3] = g->hq[(threadIdx.x - 12) / 3][(threadIdx.x - 12) % 3];
     else if (threadIdx.x == 21) dt_s = g->dt;
@@ -312,7 +343,7 @@ __global__ void __launch_bounds__(kThreads, CF_HJ_UPDATE_MIN_BLOCKS) k_update(co
 #pragma unroll
     for (int d = 0; d < 6; ++d) dV[d] = mul(add(L[d], R[d]), 0.5f);           // (L + R) / 2: exact either way
     float f[6], base[3], a[6];
-    dynamics_parts(idx, f, base);
+    dynamics_parts(tab, idx, f, base);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         const float own = dV[3 + i] > 0.f ? hq[i][0] : (dV[3 + i] < 0.f ? hq[i][1] : hq[i][2]);
@@ -330,7 +361,12 @@ __global__ void __launch_bounds__(kThreads, CF_HJ_UPDATE_MIN_BLOCKS) k_update(co
     ds = mul(0.5f, ds);
     vn = -sub(vn, ds);
     float out = add(vc, mul(vn, dt_s));
-    const float l0 = target_l0<PTS>(idx);
+    // l0 = FasTrackTarget, float64 sum in the reference's order, rounded once (Fastrack.py:296-306)
+    double t = c_sq012[(idx[0] * CF_HJ_MAX_PTS + idx[1]) * CF_HJ_MAX_PTS + idx[2]];
+    t = __dadd_rn(t, tab.sq3[idx[3]]);
+    t = __dadd_rn(t, tab.sq4[idx[4]]);
+    t = __dadd_rn(t, tab.sq5[idx[5]]);
+    const float l0 = (float)t;
     if (out < l0) out = l0;
     Vout[c] = out;
 }
@@ -374,6 +410,17 @@ int bind(cf_hj_solver* s) {
     HJ_CU(cudaSetDevice(s->device));
     if (g_const_owner != s) {
         HJ_CU(cudaMemcpyToSymbol(c_p, &s->prob, sizeof(cf_hj_problem)));
+        static double sq012[CF_HJ_MAX_PTS * CF_HJ_MAX_PTS * CF_HJ_MAX_PTS];
+        for (int i = 0; i < CF_HJ_MAX_PTS; ++i)
+            for (int j = 0; j < CF_HJ_MAX_PTS; ++j)
+                for (int k = 0; k < CF_HJ_MAX_PTS; ++k) {
+                    volatile double t = 0.0;                 // one rounding per addition, as NumPy does it
+                    t = t + s->prob.target_sq[0][i];
+                    t = t + s->prob.target_sq[1][j];
+                    t = t + s->prob.target_sq[2][k];
+                    sq012[(i * CF_HJ_MAX_PTS + j) * CF_HJ_MAX_PTS + k] = t;
+                }
+        HJ_CU(cudaMemcpyToSymbol(c_sq012, sq012, sizeof(sq012)));
         g_const_owner = s;
     }
     return CF_OK;
