@@ -39,6 +39,12 @@ BYTES_PER_ENV_STEP = 216 + 216 + 56 + 16 + 136 + 4 + 1 + 4 + 1
 TRAFFIC_NCU = 42.41e6
 
 
+try:
+    _ORIG_AFFINITY = os.sched_getaffinity(0)                  # the CPU baseline runs on all of these, bound or not
+except AttributeError:
+    _ORIG_AFFINITY = set(range(os.cpu_count() or 1))
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -65,6 +71,7 @@ def parse():
                     help='action source (SURVEY 8d config 3): hover + 0.05 N(0,1) resident in HBM (headline); U(-1,1) resident in HBM '
                          '(short episodes, reset-heavy); pd = on-device attitude-rate PD on the noisy obs, one extra kernel per step '
                          '(episodes run to the 500-step limit)')
+    ap.add_argument('--no-bind', action='store_true', help='do not pin the process to the CPUs local to its GPU (NVML affinity)')
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
     return ap.parse_args()
 
@@ -127,6 +134,10 @@ def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float, env_id
     V = hj_tables.synthetic_table(1.5, 15)
     for li in range(1, 21):          # one table shared by all levels: the lookup cost does not depend on its values
         co.set_table(li, V)
+    try:                                                     # all host cores again if the process was bound to the GPU's node
+        os.sched_setaffinity(0, _ORIG_AFFINITY)
+    except (AttributeError, OSError):
+        pass
     co.lib().cfo_set_num_threads(os.cpu_count() or 1)        # all host cores, whatever OMP_NUM_THREADS the launcher exported
     orc = co.OracleEnvs(cfg, envs, seed=1)
     orc.reset()
@@ -185,6 +196,9 @@ def main_ours(args):
         raise SystemExit('bench.py: no CUDA device - the product path has no CPU fallback')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    # one rank per GPU: sit on the GPU's own NUMA node before any pinned host buffer is allocated (e2e path)
+    from disturbance_crazyfile_simulation_b200 import dist_utils
+    host_binding = dist_utils.bind_to_gpu_cpus(local) if not args.no_bind else {'bound': False, 'why': '--no-bind'}
     if world > 1:
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
@@ -417,7 +431,8 @@ def main_ours(args):
             'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
                     'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,
                     'api': f'cf_step_host_async + cf_host_sync (C ABI, pinned host buffers, {D} steps in flight over the shards; '
-                           'uploads and downloads inside the timed region)'},
+                           'uploads and downloads inside the timed region)',
+                    'host_binding_rank0': host_binding},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                          'traffic': TRAFFIC_NCU, 'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
                          'avg_kernel_ms_events_per_launch': kern_ms_events,

@@ -115,3 +115,35 @@ def check_distributed_parameters(module: torch.nn.Module) -> bool:
     dist.all_reduce(lo, op=dist.ReduceOp.MIN)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     return bool(torch.allclose(lo, hi, rtol=0.0, atol=1e-6))
+
+
+def bind_to_gpu_cpus(device_index: int) -> dict:
+    """Pin the calling process to the CPUs NVML reports as local to CUDA device ``device_index`` (its NUMA node), so
+    that pinned host buffers allocated afterwards (``cf_host_alloc``) and the threads that fill them sit next to the
+    GPU's PCIe root.  One rank per GPU on a multi-socket box otherwise lands wherever the scheduler puts it, and the
+    host-pointer step path (10 MB per step per rank) crosses the socket interconnect.  Best effort: returns what was
+    done, never raises; a no-op when NVML, the affinity call or the device mapping is unavailable."""
+    import os
+    info = {'bound': False}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            h = pynvml.nvmlDeviceGetHandleByUUID(('GPU-' + uuid).encode())
+        except Exception:                                    # no uuid on this torch, or a MIG-style id
+            if os.environ.get('CUDA_VISIBLE_DEVICES'):
+                return {'bound': False, 'why': 'device mapping unknown under CUDA_VISIBLE_DEVICES'}
+            h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        ncpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        use = cpus & os.sched_getaffinity(0)
+        if use and len(use) < len(os.sched_getaffinity(0)):
+            os.sched_setaffinity(0, use)
+            info = {'bound': True, 'cpus': len(use), 'first_cpu': min(use), 'last_cpu': max(use)}
+        else:
+            info = {'bound': False, 'why': 'GPU-local CPU set is empty or already covers the process mask', 'cpus': len(use)}
+    except Exception as e:                                   # noqa: BLE001 - placement is an optimisation, never an error
+        info = {'bound': False, 'why': f'{type(e).__name__}: {e}'[:120]}
+    return info

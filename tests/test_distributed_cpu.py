@@ -166,3 +166,14 @@ def _trainer(rank, world):
 
 def test_trainer_epoch_world2():
     _run(_trainer)
+
+
+def test_bind_to_gpu_cpus_is_best_effort():
+    """No NVML / no GPU here: the placement helper reports why it did nothing and never raises."""
+    import os
+    before = os.sched_getaffinity(0)
+    info = du.bind_to_gpu_cpus(0)
+    assert isinstance(info, dict) and info['bound'] in (True, False)
+    if not info['bound']:
+        assert os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
