@@ -128,6 +128,11 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
     uint32_t* s_hj = reinterpret_cast<uint32_t*>(s_list + CF_TILE);   // [CF_TILE] landing slots of the sign-table gather (cp.async)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x, i = tile * CF_TILE + tid;
+#ifdef CF_GATHER_TO_REGISTER                                  /* tools/ only: A/B against the register-destination gather */
+    uint32_t* const my_hj = nullptr;
+#else
+    uint32_t* const my_hj = s_hj + tid;
+#endif
     float* gtile = S + (size_t)tile * (CF_STATE_WORDS * CF_TILE);
     const bool valid = i < n;
     const unsigned wmask = __ballot_sync(0xffffffffu, valid);
@@ -166,17 +171,22 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     if (tr && tid == 0) {
         asm volatile("" :: "r"(ctr0)); tr[12] = gtimer();
     }
+#ifdef CF_BARRIER_FIRST                                       /* tools/ only: A/B against the barrier in front of the draws */
+    __syncthreads();
+#endif
     DrawSrc dw0 = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
     if (valid) pregen_step_draws<NOISE, 0>(dw0, cfg, scratch, sd);   // step event of the launch's first step: counter ctr0, tag 0
     if (tr && tid == 0) tr[11] = gtimer();
+#ifndef CF_BARRIER_FIRST
     __syncthreads();                                        // mbarrier initialised, thresholds in place (first needed from here on)
+#endif
     mbar_wait(mbar, 0);
     if (tr && tid == 0) tr[2] = gtimer();
     HjFetch hjf;
     hjf.raw = 0u; hjf.shift = 0; hjf.slot = nullptr;
     if (valid) {
         consume_fresh(e, cfg, gid, NOISE);
-        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, s_hj + tid);   // the table gather is in flight behind the second half of the draws
+        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);   // the table gather is in flight behind the second half of the draws
         pregen_step_draws<NOISE, 1>(dw0, cfg, scratch, sd);
     }
     if (tr && tid == 0) tr[13] = gtimer();
@@ -188,7 +198,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (t > 0) {
                 av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
                 const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, s_hj + tid);
+                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);
                 pregen_step_draws<NOISE, 0>(dw, cfg, scratch, sd);
                 pregen_step_draws<NOISE, 1>(dw, cfg, scratch, sd);
             }
