@@ -558,6 +558,17 @@ int cf_set_state(cf_env* e, const float* state_host) {
     return CF_OK;
 }
 
+int cf_get_poses_dev(cf_env* e, const int32_t* env_idx_dev, int32_t count, float* poses_dev, void* stream) {
+    if (!e || !poses_dev || count < 0) return fail(CF_ERR_INVALID, "cf_get_poses_dev: bad argument%s", "");
+    if (count == 0) return CF_OK;
+    if (!env_idx_dev && count > e->n) return fail(CF_ERR_INVALID, "cf_get_poses_dev: count exceeds n_envs%s", "");
+    CU(cudaSetDevice(e->device));
+    launch_gather_poses(e->S, e->n, env_idx_dev, count, poses_dev, (cudaStream_t)stream);
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
 int cf_get_levels(cf_env* e, float* levels_host) {
     if (!e || !levels_host) return fail(CF_ERR_INVALID, "cf_get_levels: null argument%s", "");
     CU(cudaSetDevice(e->device));

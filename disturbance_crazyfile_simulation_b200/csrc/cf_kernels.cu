@@ -533,6 +533,21 @@ void launch_unpack_state(const float* S, int n, float* rec, cudaStream_t st) {
 void launch_pack_state(float* S, int n, const float* rec, cudaStream_t st) {
     k_pack_state<<<blocks_for(n, 128), 128, 0, st>>>(S, n, rec);
 }
+// pose rows (pos xyz, quat xyzw) of `count` envs for the rasteriser; idx == nullptr: envs 0..count-1
+__global__ void k_gather_poses(const float* __restrict__ S, int n, const int* __restrict__ idx, int count, float* __restrict__ poses) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    int i = idx ? idx[j] : j;
+    i = min(max(i, 0), n - 1);
+    const EnvRef g{env_global(const_cast<float*>(S), i)};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) poses[7 * j + k] = g.f(CF_S_POS + k);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) poses[7 * j + 3 + k] = g.f(CF_S_QUAT + k);
+}
+void launch_gather_poses(const float* S, int n, const int* idx, int count, float* poses, cudaStream_t st) {
+    k_gather_poses<<<blocks_for(count, 128), 128, 0, st>>>(S, n, idx, count, poses);
+}
 void launch_levels(const float* S, int n, float* out, cudaStream_t st) {
     k_levels<<<blocks_for(n, 128), 128, 0, st>>>(S, n, out);
 }

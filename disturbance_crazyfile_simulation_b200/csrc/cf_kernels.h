@@ -18,6 +18,7 @@ void launch_hj_lookup_f32(const float* states, int n, const DevCfg& cfg, const f
 void launch_unpack_state(const float* S, int n, float* rec, cudaStream_t st);
 void launch_pack_state(float* S, int n, const float* rec, cudaStream_t st);
 void launch_levels(const float* S, int n, float* out, cudaStream_t st);
+void launch_gather_poses(const float* S, int n, const int* idx, int count, float* poses, cudaStream_t st);
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int T, int N, float* adv, float* tgt, float* disc_ret,
                 cudaStream_t st);

@@ -113,6 +113,7 @@ class CrazyFlieVecEnv:
         self._cost = torch.empty((n,), dtype=torch.float32, device=self.device)
         self._trunc = torch.empty((n,), dtype=torch.uint8, device=self.device)
         self._term = torch.zeros((n, od), dtype=torch.float32, device=self.device) if return_terminal_obs else None
+        self._raster = None                          # frames: created on first use (capture_image / render)
         self._table_owner = share_tables_with        # keeps the owner alive
         if share_tables_with is not None:
             abi.check(L.cf_share_hj_tables(self._h, share_tables_with._h))
@@ -188,10 +189,53 @@ class CrazyFlieVecEnv:
         abi.check(self._L.cf_get_levels(self._h, out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def render(self, mode='human'):
-        raise NotImplementedError('graphics (PyBullet GUI / OpenGL camera, envs/base.py:343-418) is unavailable on this box')
+    # ------------------------------------------------------------------ frames
+    def set_visual_mesh(self, tris: np.ndarray, rgb: np.ndarray, bound_radius: Optional[float] = None) -> None:
+        """Body-frame triangle soup the frames show (default: raster.proxy_mesh()); e.g. raster.mesh_with_stl_props(dir)."""
+        from . import raster
+        r = float(np.linalg.norm(np.asarray(tris).reshape(-1, 3), axis=1).max() * 1.001) if bound_radius is None else bound_radius
+        if self._raster is not None:
+            self._raster.close()
+        self._raster = raster.Rasteriser(self.device_index, (tris, rgb, r))
 
-    capture_image = render
+    def _rasteriser(self):
+        from . import raster
+        if self._raster is None:
+            self._raster = raster.Rasteriser(self.device_index)
+        return self._raster
+
+    def poses(self, indices: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Device tensor [F, 7]: position xyz + quaternion xyzw of the envs ``indices`` (int32 CUDA tensor; default all)."""
+        dev = self.device
+        if indices is None:
+            idx, n = None, self.num_envs
+        else:
+            idx = indices.to(device=dev, dtype=torch.int32).contiguous()
+            n = idx.numel()
+        out = torch.empty((n, 7), dtype=torch.float32, device=dev)
+        abi.check(self._L.cf_get_poses_dev(self._h, _ptr(idx), n, _ptr(out), self._stream()))
+        return out
+
+    def capture_images(self, indices: Optional[torch.Tensor] = None, camera=None) -> torch.Tensor:
+        """uint8 CUDA tensor [F, 1080, 1920, 3]: one ``capture_image()`` frame per env in ``indices``, one launch."""
+        with torch.cuda.device(self.device):
+            return self._rasteriser().render(self.poses(indices), camera=camera)
+
+    def capture_image(self, index: int = 0) -> np.ndarray:
+        """``capture_image()`` of the reference (envs/base.py:520-544): [1080, 1920, 3] uint8, camera following the drone."""
+        idx = torch.tensor([index], dtype=torch.int32, device=self.device)
+        return self.capture_images(idx)[0].cpu().numpy()
+
+    def render(self, mode='human', index: int = 0):
+        """``render('rgb_array')`` (envs/base.py:379-416): the fixed camera at the origin.  'human' opens the PyBullet
+        GUI in the reference; graphics is unavailable on this box."""
+        if mode == 'rgb_array':
+            from . import raster
+            idx = torch.tensor([index], dtype=torch.int32, device=self.device)
+            return self.capture_images(idx, camera=raster.render_camera())[0].cpu().numpy()
+        if mode == 'human':
+            raise NotImplementedError('render("human") is the PyBullet GUI (envs/base.py:364-377): unavailable on this box')
+        raise NotImplementedError(mode)
 
     # ------------------------------------------------------------------ state / parity hooks
     def get_state(self) -> np.ndarray:
@@ -278,6 +322,9 @@ class CrazyFlieVecEnv:
         abi.check(self._L.cf_host_sync(self._h))
 
     def close(self):
+        if getattr(self, '_raster', None) is not None:
+            self._raster.close()
+            self._raster = None
         if getattr(self, '_h', None) is not None and self._h.value:
             self._L.cf_destroy(self._h)
             self._h = C.c_void_p()
@@ -331,6 +378,9 @@ class GymAdapter:
 
     def render(self, mode='human'):
         return self.vec.render(mode)
+
+    def capture_image(self) -> np.ndarray:
+        return self.vec.capture_image(0)
 
     def close(self):
         self.vec.close()

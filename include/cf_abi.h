@@ -264,6 +264,48 @@ int cf_hj_solver_run(cf_hj_solver* s, double lookback, double t_step, int64_t ma
 /* average device time of one update (all its kernels) over the updates run so far, in ms */
 int cf_hj_solver_timing(cf_hj_solver* s, double* avg_ms_per_update, int64_t* updates);
 
+/* ---- f4: headless rasteriser ---------------------------------------------------------------------
+ * Replaces BulletClient.getCameraImage(..., renderer=ER_BULLET_HARDWARE_OPENGL) behind the reference's
+ * `capture_image()` (envs/base.py:520-544) and `render('rgb_array')` (envs/base.py:379-416): 1920x1080x3 uint8
+ * frames of the drone over the ground plane, written into a device buffer - no graphics API involved (graphics
+ * is unavailable on this box).  The camera is the one those calls build: computeViewMatrixFromYawPitchRoll
+ * (target = drone position, distance 1.8, yaw 10, pitch -20, roll 0, up axis z) and computeProjectionMatrixFOV
+ * (fov 60, aspect w/h, near 0.1); the host derives the basis below from those numbers (raster.py).
+ * The drone is a triangle soup in the body frame (the URDF's visual meshes loaded by the host, or the built-in
+ * proxy made of the URDF's collision shapes); triangles are flat-shaded, two-sided, z-tested per pixel; a triangle
+ * with a vertex in front of the near plane is dropped, not clipped.  The ground is the z = 0 plane out to
+ * +-ground_half metres with a procedural checker.  All arithmetic is float32 without fused multiply-adds so that
+ * oracle/raster_oracle.py reproduces every byte. */
+typedef struct cf_camera {
+    int32_t width, height;       /* width % 4 == 0 */
+    int32_t follow;              /* 1: target = the frame's drone position (capture_image); 0: target[] (render) */
+    float target[3];
+    float eye_offset[3];         /* eye = target + eye_offset */
+    float right[3], up[3], fwd[3];   /* orthonormal camera basis in the world frame */
+    float tan_x, tan_y;          /* tan(fov/2) * aspect, tan(fov/2) */
+    float near_plane;
+    float light[3];              /* unit vector towards the light */
+    float ambient, diffuse;
+    float background[3], ground_a[3], ground_b[3];   /* colours in 0..1 */
+    float inv_checker;           /* 1 / edge of a ground square, 1/m */
+    float ground_half;           /* half extent of the ground plane, m */
+} cf_camera;
+
+typedef struct cf_raster cf_raster;
+/* tris_host [n_tris][3][3] body-frame vertices, rgb_host [n_tris][3] colours in 0..1 (both copied);
+ * bound_radius >= the largest vertex norm (used only to skip pixel blocks the drone cannot touch) */
+int cf_raster_create(cf_raster** out, int32_t device, const float* tris_host, const float* rgb_host, int32_t n_tris,
+                     float bound_radius);
+void cf_raster_destroy(cf_raster* r);
+/* poses_dev [n_frames][7] = position xyz, quaternion xyzw (DEVICE); rgb_dev [n_frames][height][width][3] uint8 (DEVICE);
+ * asynchronous on `stream` (a cudaStream_t, NULL = default stream) */
+int cf_raster_render_dev(cf_raster* r, const cf_camera* cam, const float* poses_dev, int32_t n_frames, uint8_t* rgb_dev,
+                         void* stream);
+/* the same with HOST buffers; synchronous */
+int cf_raster_render_host(cf_raster* r, const cf_camera* cam, const float* poses_host, int32_t n_frames, uint8_t* rgb_host);
+/* pose rows of envs env_idx_dev[0..count) (DEVICE int32; NULL = envs 0..count-1) into poses_dev [count][7] (DEVICE) */
+int cf_get_poses_dev(cf_env* env, const int32_t* env_idx_dev, int32_t count, float* poses_dev, void* stream);
+
 /* ---- pinned host memory for the host-pointer API (so its copies are asynchronous DMA) ------- */
 void* cf_host_alloc(uint64_t bytes);     /* NULL on failure (cf_last_error) */
 void cf_host_free(void* p);
