@@ -369,6 +369,30 @@ def main_ours(args):
                                      'latency / instruction bound (13-point 6-D stencil, IEEE divisions kept for exactness), '
                                      'not HBM bound'}
         hs.close()
+        # (e) frames of capture_image(): 64 frames of 1920x1080x3 uint8 per launch, poses resident on the
+        # device; algorithmic bytes = the frame buffer written once (3 B per pixel)
+        from disturbance_crazyfile_simulation_b200 import raster
+        rs = raster.Rasteriser(local)
+        n_fr = 64
+        rp = torch.zeros((n_fr, 7), device=dev)
+        rp[:, :3] = torch.rand((n_fr, 3), device=dev) * 2 - 1
+        rp[:, 2] = rp[:, 2].abs() + 0.3
+        rp[:, 3:] = torch.nn.functional.normalize(torch.randn((n_fr, 4), device=dev), dim=1)
+        r_out = torch.empty((n_fr, 1080, 1920, 3), dtype=torch.uint8, device=dev)
+        for _ in range(3):
+            rs.render(rp, out=r_out)
+        ev0.record()
+        for _ in range(10):
+            rs.render(rp, out=r_out)
+        ev1.record(); torch.cuda.synchronize()
+        r_ms = ev0.elapsed_time(ev1) / 10
+        side['raster'] = {'frames_per_launch': n_fr, 'triangles': rs.n_tris, 'ms_per_launch': r_ms,
+                          'frames_per_s': n_fr / (r_ms * 1e-3), 'bytes_per_frame': 1080 * 1920 * 3,
+                          'achieved_gb_s': n_fr * 1080 * 1920 * 3 / (r_ms * 1e-3) / 1e9,
+                          'note': 'byte-identical to oracle/raster_oracle.py; parity with PyBullet OpenGL frames unpinned '
+                                  '(graphics unavailable on this box)'}
+        rs.close()
+        del r_out
 
     # ---- e2e: the public host-pointer API (cf_step_host) with pinned HOST buffers ---------------
     def pinned(shape, dtype):

@@ -64,7 +64,7 @@ __global__ void k_frame_ctx(const __grid_constant__ cf_camera cam, float radius,
     const int frame = blockIdx.x * blockDim.x + threadIdx.x;
     if (frame >= n_frames) return;
     FrameCtx fc;
-    const float half_w = D((float)cam.width, 2.f), half_h = D((float)cam.height, 2.f);
+    const float half_w = M((float)cam.width, 0.5f), half_h = M((float)cam.height, 0.5f);
     const float* ps = poses + 7 * (size_t)frame;
     const float x = ps[3], y = ps[4], z = ps[5], w = ps[6];
     const float xx = M(x, x), yy = M(y, y), zz = M(z, z), xy = M(x, y), xz = M(x, z), yz = M(y, z), wx = M(w, x), wy = M(w, y), wz = M(w, z);
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(NT) k_raster(const float* __restrict__ tris, c
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
     const int frame = blockIdx.z, bx0 = blockIdx.x * BW, by0 = blockIdx.y * BH;
     const int W = cam.width, H = cam.height;
-    const float half_w = D((float)W, 2.f), half_h = D((float)H, 2.f);
+    const float half_w = M((float)W, 0.5f), half_h = M((float)H, 0.5f);          // == W / 2, H / 2
     static_assert(sizeof(FrameCtx) % 4 == 0 && sizeof(FrameCtx) / 4 <= NT, "context copy");
     if (tid < (int)(sizeof(FrameCtx) / 4)) reinterpret_cast<uint32_t*>(&fc)[tid] = reinterpret_cast<const uint32_t*>(ctx + frame)[tid];
     __syncthreads();
@@ -117,11 +117,12 @@ __global__ void __launch_bounds__(NT) k_raster(const float* __restrict__ tris, c
     const float cxr = A(cam.fwd[0], M(cam.up[0], tyv)), cyr = A(cam.fwd[1], M(cam.up[1], tyv)), czr = A(cam.fwd[2], M(cam.up[2], tyv));
     const bool flat = cam.right[2] == 0.f, above = fc.eye[2] > 0.f;
     const float t_row = (flat && above && czr < 0.f) ? D(fc.eye[2], -czr) : 0.f;
+    const float pxc0 = A((float)px0, 0.5f);
     uint32_t col[4];
     float tg[4];                                            // depth of the ground hit along the view axis (0: none)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const float pxc = A((float)(px0 + j), 0.5f);
+        const float pxc = A(pxc0, (float)j);                // == (px0 + j) + 0.5 exactly (integers below 2^24)
         const float txv = M(Sb(M(pxc, ihw), 1.f), cam.tan_x);
         const float dx = A(cxr, M(cam.right[0], txv)), dy = A(cyr, M(cam.right[1], txv));
         const float dz = flat ? czr : A(czr, M(cam.right[2], txv));
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(NT) k_raster(const float* __restrict__ tris, c
             const float t = flat ? t_row : D(fc.eye[2], -dz);
             const float hx = A(fc.eye[0], M(t, dx)), hy = A(fc.eye[1], M(t, dy));
             if (fabsf(hx) <= cam.ground_half && fabsf(hy) <= cam.ground_half) {
-                const int ix = (int)floorf(M(hx, cam.inv_checker)), iy = (int)floorf(M(hy, cam.inv_checker));
+                const int ix = __float2int_rd(M(hx, cam.inv_checker)), iy = __float2int_rd(M(hy, cam.inv_checker));   // floor
                 col[j] = ((ix + iy) & 1) ? fc.gb : fc.ga;
                 tg[j] = t;
             }
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(NT) k_raster(const float* __restrict__ tris, c
                 const int id = __float_as_int(c.w);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float pxc = A((float)(px0 + j), 0.5f);
+                    const float pxc = A(pxc0, (float)j);
                     const float b0 = M(Sb(M(Sb(pxc, x1), e0y), r0), ia);
                     const float b1 = M(Sb(M(Sb(pxc, x2), e1y), r1), ia);
                     const float b2 = M(Sb(M(Sb(pxc, x0), e2y), r2), ia);
