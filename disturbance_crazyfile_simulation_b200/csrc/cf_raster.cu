@@ -4,21 +4,24 @@
 // envs/base.py:520-544 (capture_image, one call per control step of a validation episode, iwpg.py:513-536) and
 // envs/base.py:379-416 (render).  No graphics API: frames are written into a device buffer.
 //
-// Two launches for all frames of a batch: k_frame_ctx (one thread per frame: eye, rotation matrix, colours, the
-// drone's screen-space bound) and k_raster, where a CTA owns a 128 x 8 pixel block of one frame (4 pixels per
-// thread, so a warp writes 384 contiguous bytes of a row):
-//   1. the frame's context is copied into shared memory;
-//   2. every pixel gets the background or the ground checker from its view ray (closed form, no geometry);
-//   3. only CTAs the drone's bounding sphere can touch walk the triangle soup in chunks of 256: each thread sets
-//      one triangle up (body -> world -> camera -> pixel coordinates, flat Lambert colour), triangles whose bounding
-//      box misses the CTA's block are dropped, the rest are compacted into shared memory and every thread tests its
-//      four pixel centres against them (edge functions, 1/z interpolated with the barycentrics, nearest wins,
-//      equal depth -> lower triangle index, so the result does not depend on the compaction order);
-//   4. 12 bytes per thread leave as three 32-bit stores.
+// Four launches for all frames of a batch:
+//   k_frame_ctx   one thread per frame: eye, rotation matrix, packed sky / ground colours, the screen-space bound of the
+//                 drone's bounding sphere;
+//   k_background  every pixel gets the sky or the ground checker from its view ray in closed form: a CTA owns 128 x 32
+//                 pixels, a thread 4 columns x 4 rows, so a warp writes 384 contiguous bytes of a row and everything
+//                 that depends on the column only is computed once; no shared memory, no barrier;
+//   k_tri_setup   one thread per (frame, triangle): body -> world -> camera -> pixel coordinates, flat Lambert colour,
+//                 a 48-byte record + a bounding box;
+//   k_raster      only over the 32 x 8 pixel blocks the bounding sphere can touch (for follow cameras the grid is a
+//                 small window hung at the sphere's screen bound): one pixel per thread, a warp owns a compact 8 x 4
+//                 patch, scans the frame's bounding boxes 32 at a time and tests its pixel centres against the
+//                 triangles that reach the patch (edge functions, 1/z interpolated with the barycentrics, nearest wins,
+//                 equal depth -> lower triangle index, so the result does not depend on any order of evaluation).
 // Bound: HBM writes, 3 bytes per pixel (6.2 MB per 1920x1080 frame); the triangle data (a few hundred KB) lives in L2.
 // Arithmetic: float32 through the non-contracting intrinsics, mirrored operation by operation by
 // oracle/raster_oracle.py (NumPy float32), which the parity tests compare with byte for byte.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 
 #include <new>
@@ -33,11 +36,13 @@ struct cf_raster {
     float* rgb = nullptr;        // [n_tris][3]
     void* ctx = nullptr;         // [ctx_frames] FrameCtx, written by k_frame_ctx in front of every k_raster launch
     int ctx_frames = 0;
+    void* rec = nullptr;         // [rec_frames][n_tris] TriRec + [rec_frames][n_tris] float4 boxes, written by k_tri_setup
+    int rec_frames = 0;
 };
 
 namespace {
 
-constexpr int BW = 128, BH = 8, NT = 256, CHUNK = 256;
+constexpr int BW = 128, BH = 8, NT = 256;
 
 __device__ __forceinline__ float M(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float A(float a, float b) { return __fadd_rn(a, b); }
@@ -54,6 +59,8 @@ struct FrameCtx {
     float pos[3], R[9], eye[3];
     float cx, cy, rad;           // screen-space bound of the drone (pixels); rad < 0: whole screen
     uint32_t bg, ga, gb;         // packed colours: background, the two ground squares (already shaded)
+    float ihw, ihh;              // 2 / width, 2 / height
+    int bx0, bx1, by0, by1;      // pixel bounds of the triangles that survive set-up (k_tri_setup: atomicMin / atomicMax)
 };
 
 struct TriRec { float4 a, b, c; };   // (x0 y0 x1 y1) (x2 y2 1/area 1/z0) (1/z1 1/z2 rgb idx)
@@ -90,145 +97,241 @@ __global__ void k_frame_ctx(const __grid_constant__ cf_camera cam, float radius,
     fc.bg = pack_rgb(cam.background[0], cam.background[1], cam.background[2]);
     fc.ga = pack_rgb(M(cam.ground_a[0], sg), M(cam.ground_a[1], sg), M(cam.ground_a[2], sg));
     fc.gb = pack_rgb(M(cam.ground_b[0], sg), M(cam.ground_b[1], sg), M(cam.ground_b[2], sg));
+    fc.ihw = D(2.f, (float)cam.width);
+    fc.ihh = D(2.f, (float)cam.height);
+    fc.bx0 = fc.by0 = 0x7fffffff;
+    fc.bx1 = fc.by1 = -0x7fffffff - 1;
     ctx[frame] = fc;
 }
 
-__global__ void __launch_bounds__(NT) k_raster(const float* __restrict__ tris, const float* __restrict__ rgb, int n_tris,
-                                               const __grid_constant__ cf_camera cam, const FrameCtx* __restrict__ ctx,
-                                               uint8_t* __restrict__ out) {
-    __shared__ FrameCtx fc;
-    __shared__ TriRec s_tri[CHUNK];
-    __shared__ int s_cnt;
+// Background and ground of every pixel: a CTA owns 128 x 32 pixels of one frame; a thread owns 4 columns x 4 rows
+// (rows ty, ty + 8, ty + 16, ty + 24 of the block), so everything that depends on the column only is computed once and
+// a warp still writes 384 contiguous bytes of a row.  No shared memory, no barrier.
+constexpr int GH = 32, GROWS = GH / BH;
+__device__ __forceinline__ float keep(float v) { asm volatile("" : "+f"(v)); return v; }   // held in a register, not recomputed
+template <bool FLAT>                                        // FLAT: camera without roll (right_z == 0)
+__global__ void __launch_bounds__(NT) k_background(const __grid_constant__ cf_camera cam, const FrameCtx* __restrict__ ctx,
+                                                   uint8_t* __restrict__ out) {
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
-    const int frame = blockIdx.z, bx0 = blockIdx.x * BW, by0 = blockIdx.y * BH;
+    const int frame = blockIdx.z, px0 = blockIdx.x * BW + 4 * tx, by0 = blockIdx.y * GH;
     const int W = cam.width, H = cam.height;
-    const float half_w = M((float)W, 0.5f), half_h = M((float)H, 0.5f);          // == W / 2, H / 2
-    static_assert(sizeof(FrameCtx) % 4 == 0 && sizeof(FrameCtx) / 4 <= NT, "context copy");
-    if (tid < (int)(sizeof(FrameCtx) / 4)) reinterpret_cast<uint32_t*>(&fc)[tid] = reinterpret_cast<const uint32_t*>(ctx + frame)[tid];
-    __syncthreads();
-
-    // ---- background / ground from the view ray --------------------------------------------------
-    const int px0 = bx0 + 4 * tx, py = by0 + ty;
-    const float pyc = A((float)py, 0.5f);
-    const float ihw = D(2.f, (float)W), ihh = D(2.f, (float)H);
-    const float tyv = M(Sb(1.f, M(pyc, ihh)), cam.tan_y);
-    // view ray d = (fwd + up * tyv) + right * txv: the bracket is constant along the thread's row; without camera roll
-    // right_z == 0, so d_z and the ground depth t = eye_z / -d_z are too (A(c, M(0, txv)) == c: an exact rewrite)
-    const float cxr = A(cam.fwd[0], M(cam.up[0], tyv)), cyr = A(cam.fwd[1], M(cam.up[1], tyv)), czr = A(cam.fwd[2], M(cam.up[2], tyv));
-    const bool flat = cam.right[2] == 0.f, above = fc.eye[2] > 0.f;
-    const float t_row = (flat && above && czr < 0.f) ? D(fc.eye[2], -czr) : 0.f;
+    if (px0 >= W) return;
+    const FrameCtx* c = ctx + frame;
+    const float ex = keep(__ldg(&c->eye[0])), ey = keep(__ldg(&c->eye[1])), ez = __ldg(&c->eye[2]);
+    const float ihw = __ldg(&c->ihw), ihh = __ldg(&c->ihh);
+    const uint32_t bg = __ldg(&c->bg), ga = __ldg(&c->ga), gb = __ldg(&c->gb);
+    const bool above = ez > 0.f;
+    const float gh = keep(cam.ground_half), ick = keep(cam.inv_checker);
     const float pxc0 = A((float)px0, 0.5f);
-    uint32_t col[4];
-    float tg[4];                                            // depth of the ground hit along the view axis (0: none)
+    float rx[4], ry[4], rz[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const float pxc = A(pxc0, (float)j);                // == (px0 + j) + 0.5 exactly (integers below 2^24)
-        const float txv = M(Sb(M(pxc, ihw), 1.f), cam.tan_x);
-        const float dx = A(cxr, M(cam.right[0], txv)), dy = A(cyr, M(cam.right[1], txv));
-        const float dz = flat ? czr : A(czr, M(cam.right[2], txv));
-        col[j] = fc.bg;
-        tg[j] = 0.f;
-        if (dz < 0.f && above) {
-            const float t = flat ? t_row : D(fc.eye[2], -dz);
-            const float hx = A(fc.eye[0], M(t, dx)), hy = A(fc.eye[1], M(t, dy));
-            if (fabsf(hx) <= cam.ground_half && fabsf(hy) <= cam.ground_half) {
-                const int ix = __float2int_rd(M(hx, cam.inv_checker)), iy = __float2int_rd(M(hy, cam.inv_checker));   // floor
-                col[j] = ((ix + iy) & 1) ? fc.gb : fc.ga;
-                tg[j] = t;
-            }
-        }
+        const float txv = M(Sb(M(A(pxc0, (float)j), ihw), 1.f), cam.tan_x);
+        rx[j] = keep(M(cam.right[0], txv)); ry[j] = keep(M(cam.right[1], txv));
+        rz[j] = FLAT ? 0.f : keep(M(cam.right[2], txv));
     }
-
-    // ---- the drone ----------------------------------------------------------------------------------
-    const bool touched = fc.rad < 0.f || ((float)bx0 <= fc.cx + fc.rad && (float)(bx0 + BW) >= fc.cx - fc.rad &&
-                                          (float)by0 <= fc.cy + fc.rad && (float)(by0 + BH) >= fc.cy - fc.rad);
-    if (touched) {                                          // uniform over the CTA
-        float best[4];
-        int best_id[4];
+    uint8_t* obase = out + ((size_t)frame * H) * (size_t)W * 3 + (size_t)px0 * 3;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { best[j] = tg[j] > 0.f ? D(1.f, tg[j]) : 0.f; best_id[j] = 0x7fffffff; }
-        for (int c0 = 0; c0 < n_tris; c0 += CHUNK) {
-            if (tid == 0) s_cnt = 0;
-            __syncthreads();
-            const int ti = c0 + tid;
-            if (ti < n_tris) {
-                const float* tv = tris + 9 * (size_t)ti;
-                float wv[3][3], sx[3], sy[3], iz[3];
-                bool ok = true;
-#pragma unroll
-                for (int v = 0; v < 3; ++v) {
-                    const float bx = tv[3 * v], by = tv[3 * v + 1], bz = tv[3 * v + 2];
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) wv[v][k] = A(fc.pos[k], dot3(bx, by, bz, fc.R + 3 * k) );
-                    float pc[3];
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) pc[k] = Sb(wv[v][k], fc.eye[k]);
-                    const float xc = dot3(pc, cam.right), yc = dot3(pc, cam.up), zc = dot3(pc, cam.fwd);
-                    ok = ok && zc >= cam.near_plane;
-                    sx[v] = M(A(D(D(xc, zc), cam.tan_x), 1.f), half_w);
-                    sy[v] = M(Sb(1.f, D(D(yc, zc), cam.tan_y)), half_h);
-                    iz[v] = D(1.f, zc);
-                }
-                const float area = Sb(M(Sb(sx[2], sx[0]), Sb(sy[1], sy[0])), M(Sb(sy[2], sy[0]), Sb(sx[1], sx[0])));
-                ok = ok && area != 0.f;
-                const float mnx = fminf(sx[0], fminf(sx[1], sx[2])), mxx = fmaxf(sx[0], fmaxf(sx[1], sx[2]));
-                const float mny = fminf(sy[0], fminf(sy[1], sy[2])), mxy = fmaxf(sy[0], fmaxf(sy[1], sy[2]));
-                // pixel centres of the block span [bx0 + .5, bx0 + BW - .5]; one pixel of slack
-                ok = ok && mnx <= (float)(bx0 + BW) + 0.5f && mxx >= (float)bx0 - 0.5f && mny <= (float)(by0 + BH) + 0.5f &&
-                     mxy >= (float)by0 - 0.5f;
-                if (ok) {
-                    float e1[3], e2[3], ev[3], n[3];
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) { e1[k] = Sb(wv[1][k], wv[0][k]); e2[k] = Sb(wv[2][k], wv[0][k]); ev[k] = Sb(fc.eye[k], wv[0][k]); }
-                    n[0] = Sb(M(e1[1], e2[2]), M(e1[2], e2[1]));
-                    n[1] = Sb(M(e1[2], e2[0]), M(e1[0], e2[2]));
-                    n[2] = Sb(M(e1[0], e2[1]), M(e1[1], e2[0]));
-                    const float len = __fsqrt_rn(dot3(n, n));
-                    if (len > 0.f) {
-                        float ndl = D(dot3(n, cam.light), len);
-                        if (dot3(n, ev) < 0.f) ndl = -ndl;      // two-sided: the normal is turned towards the eye
-                        const float sh = A(cam.ambient, M(cam.diffuse, fmaxf(ndl, 0.f)));
-                        const float* cr = rgb + 3 * (size_t)ti;
-                        const uint32_t pk = pack_rgb(M(cr[0], sh), M(cr[1], sh), M(cr[2], sh));
-                        const int slot = atomicAdd(&s_cnt, 1);
-                        s_tri[slot].a = make_float4(sx[0], sy[0], sx[1], sy[1]);
-                        s_tri[slot].b = make_float4(sx[2], sy[2], D(1.f, area), iz[0]);
-                        s_tri[slot].c = make_float4(iz[1], iz[2], __uint_as_float(pk), __int_as_float(ti));
-                    }
-                }
-            }
-            __syncthreads();
-            const int cnt = s_cnt;
-            for (int r = 0; r < cnt; ++r) {
-                const float4 a = s_tri[r].a, b = s_tri[r].b, c = s_tri[r].c;
-                const float x0 = a.x, y0 = a.y, x1 = a.z, y1 = a.w, x2 = b.x, y2 = b.y, ia = b.z;
-                const float e0x = Sb(x2, x1), e0y = Sb(y2, y1), e1x = Sb(x0, x2), e1y = Sb(y0, y2), e2x = Sb(x1, x0), e2y = Sb(y1, y0);
-                const float r0 = M(Sb(pyc, y1), e0x), r1 = M(Sb(pyc, y2), e1x), r2 = M(Sb(pyc, y0), e2x);
-                const int id = __float_as_int(c.w);
+    for (int r = 0; r < GROWS; ++r) {
+        const int py = by0 + ty + BH * r;
+        if (py >= H) break;
+        const float tyv = M(Sb(1.f, M(A((float)py, 0.5f), ihh)), cam.tan_y);
+        const float cxr = A(cam.fwd[0], M(cam.up[0], tyv)), cyr = A(cam.fwd[1], M(cam.up[1], tyv)), czr = A(cam.fwd[2], M(cam.up[2], tyv));
+        uint32_t col[4] = {bg, bg, bg, bg};
+        if (FLAT) {                                         // the whole row is ground or sky: one division per row, selects per pixel
+            if (above && czr < 0.f) {
+                const float t = D(ez, -czr);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float pxc = A(pxc0, (float)j);
-                    const float b0 = M(Sb(M(Sb(pxc, x1), e0y), r0), ia);
-                    const float b1 = M(Sb(M(Sb(pxc, x2), e1y), r1), ia);
-                    const float b2 = M(Sb(M(Sb(pxc, x0), e2y), r2), ia);
-                    if (b0 >= 0.f && b1 >= 0.f && b2 >= 0.f) {
-                        const float izp = A(A(M(b0, b.w), M(b1, c.x)), M(b2, c.y));
-                        if (izp > best[j] || (izp == best[j] && id < best_id[j])) {
-                            best[j] = izp; best_id[j] = id; col[j] = __float_as_uint(c.z);
-                        }
-                    }
+                    const float hx = A(ex, M(t, A(cxr, rx[j]))), hy = A(ey, M(t, A(cyr, ry[j])));
+                    const uint32_t g = ((__float2int_rd(M(hx, ick)) + __float2int_rd(M(hy, ick))) & 1) ? gb : ga;
+                    col[j] = (fabsf(hx) <= gh && fabsf(hy) <= gh) ? g : bg;
                 }
             }
-            __syncthreads();                                // the chunk is overwritten by the next one
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float dz = A(czr, rz[j]);
+                if (dz < 0.f && above) {
+                    const float t = D(ez, -dz);
+                    const float hx = A(ex, M(t, A(cxr, rx[j]))), hy = A(ey, M(t, A(cyr, ry[j])));
+                    if (fabsf(hx) <= gh && fabsf(hy) <= gh)
+                        col[j] = ((__float2int_rd(M(hx, ick)) + __float2int_rd(M(hy, ick))) & 1) ? gb : ga;
+                }
+            }
         }
-    }
-
-    // ---- 4 pixels = 12 bytes = three words -------------------------------------------------------
-    if (px0 < W && py < H) {
-        uint32_t* o = reinterpret_cast<uint32_t*>(out + ((size_t)frame * H + py) * (size_t)W * 3 + (size_t)px0 * 3);
+        uint32_t* o = reinterpret_cast<uint32_t*>(obase + (size_t)py * (size_t)W * 3);
         o[0] = col[0] | (col[1] << 24);
         o[1] = (col[1] >> 8) | (col[2] << 16);
         o[2] = (col[2] >> 16) | (col[3] << 8);
+    }
+}
+
+// ---- drone pass ------------------------------------------------------------------------------------------------
+// k_tri_setup: one thread per (frame, triangle): body -> world -> camera -> pixel coordinates, flat Lambert colour;
+// writes a 48-byte record and a bounding box (an empty box for a triangle that is dropped).
+__global__ void __launch_bounds__(NT) k_tri_setup(const float* __restrict__ tris, const float* __restrict__ rgb, int n_tris,
+                                                  const __grid_constant__ cf_camera cam, FrameCtx* __restrict__ ctx,
+                                                  TriRec* __restrict__ rec, float4* __restrict__ bbs) {
+    const int frame = blockIdx.y;
+    const bool valid = (int)(blockIdx.x * NT + threadIdx.x) < n_tris;       // the tail threads redo the last triangle and write nothing
+    const int ti = valid ? blockIdx.x * NT + threadIdx.x : n_tris - 1;
+    FrameCtx* c = ctx + frame;
+    float pos[3], eye[3], R[9];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { pos[k] = __ldg(&c->pos[k]); eye[k] = __ldg(&c->eye[k]); }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) R[k] = __ldg(&c->R[k]);
+    const float half_w = M((float)cam.width, 0.5f), half_h = M((float)cam.height, 0.5f);      // == W / 2, H / 2
+    const float* tv = tris + 9 * (size_t)ti;
+    float wv[3][3], sx[3], sy[3], iz[3];
+    bool ok = true;
+#pragma unroll
+    for (int v = 0; v < 3; ++v) {
+        const float bx = tv[3 * v], by = tv[3 * v + 1], bz = tv[3 * v + 2];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) wv[v][k] = A(pos[k], dot3(bx, by, bz, R + 3 * k));
+        float pc[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) pc[k] = Sb(wv[v][k], eye[k]);
+        const float xc = dot3(pc, cam.right), yc = dot3(pc, cam.up), zc = dot3(pc, cam.fwd);
+        ok = ok && zc >= cam.near_plane;
+        sx[v] = M(A(D(D(xc, zc), cam.tan_x), 1.f), half_w);
+        sy[v] = M(Sb(1.f, D(D(yc, zc), cam.tan_y)), half_h);
+        iz[v] = D(1.f, zc);
+    }
+    const float area = Sb(M(Sb(sx[2], sx[0]), Sb(sy[1], sy[0])), M(Sb(sy[2], sy[0]), Sb(sx[1], sx[0])));
+    ok = ok && area != 0.f;
+    float e1[3], e2[3], ev[3], n[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { e1[k] = Sb(wv[1][k], wv[0][k]); e2[k] = Sb(wv[2][k], wv[0][k]); ev[k] = Sb(eye[k], wv[0][k]); }
+    n[0] = Sb(M(e1[1], e2[2]), M(e1[2], e2[1]));
+    n[1] = Sb(M(e1[2], e2[0]), M(e1[0], e2[2]));
+    n[2] = Sb(M(e1[0], e2[1]), M(e1[1], e2[0]));
+    const float len = __fsqrt_rn(dot3(n, n));
+    ok = ok && len > 0.f;
+    const size_t o = (size_t)frame * n_tris + ti;
+    const float mnx = fminf(sx[0], fminf(sx[1], sx[2])), mxx = fmaxf(sx[0], fmaxf(sx[1], sx[2]));
+    const float mny = fminf(sy[0], fminf(sy[1], sy[2])), mxy = fmaxf(sy[0], fmaxf(sy[1], sy[2]));
+    {                                                       // pixel bounds of the frame's drone: warp reduction, 4 atomics per warp
+        const float lim = 1.0e9f;
+        const bool in = ok && valid;
+        const int a0 = __reduce_min_sync(0xffffffffu, in ? (int)floorf(fmaxf(mnx, -lim)) : 0x7fffffff);
+        const int a1 = __reduce_max_sync(0xffffffffu, in ? (int)ceilf(fminf(mxx, lim)) : -0x7fffffff - 1);
+        const int a2 = __reduce_min_sync(0xffffffffu, in ? (int)floorf(fmaxf(mny, -lim)) : 0x7fffffff);
+        const int a3 = __reduce_max_sync(0xffffffffu, in ? (int)ceilf(fminf(mxy, lim)) : -0x7fffffff - 1);
+        if ((threadIdx.x & 31) == 0 && a0 != 0x7fffffff) {
+            atomicMin(&c->bx0, a0); atomicMax(&c->bx1, a1); atomicMin(&c->by0, a2); atomicMax(&c->by1, a3);
+        }
+    }
+    if (!valid) return;
+    if (!ok) {                                              // empty box: no patch ever picks it
+        bbs[o] = make_float4(3.0e38f, -3.0e38f, 3.0e38f, -3.0e38f);
+        return;
+    }
+    float ndl = D(dot3(n, cam.light), len);
+    if (dot3(n, ev) < 0.f) ndl = -ndl;                      // two-sided: the normal is turned towards the eye
+    const float sh = A(cam.ambient, M(cam.diffuse, fmaxf(ndl, 0.f)));
+    const float* cr = rgb + 3 * (size_t)ti;
+    const uint32_t pk = pack_rgb(M(cr[0], sh), M(cr[1], sh), M(cr[2], sh));
+    rec[o].a = make_float4(sx[0], sy[0], sx[1], sy[1]);
+    rec[o].b = make_float4(sx[2], sy[2], D(1.f, area), iz[0]);
+    rec[o].c = make_float4(iz[1], iz[2], __uint_as_float(pk), __int_as_float(ti));
+    bbs[o] = make_float4(mnx, mxx, mny, mxy);
+}
+
+// k_raster: runs behind k_background over the pixel blocks the drone's bounding sphere can touch and rewrites them whole.
+// A CTA owns 32 x 8 pixels, one pixel per thread, a warp a compact 8 x 4 patch: the drone is ~50 pixels wide with hundreds
+// of triangles, so small patches spread the triangle walk over many warps.  No shared memory, no barrier: a warp scans the
+// frame's bounding boxes 32 at a time (one per lane) and walks only the triangles that reach its patch.
+// bounded != 0: the grid is a window of blocks hung at the sphere's screen bound (follow cameras, where the host knows its
+// size); else the grid covers the frame and untouched CTAs leave at once.
+constexpr int RW = 32, RH = 8;
+__global__ void __launch_bounds__(NT) k_raster(int n_tris, const __grid_constant__ cf_camera cam, const FrameCtx* __restrict__ ctx,
+                                               const TriRec* __restrict__ rec, const float4* __restrict__ bbs, int bounded,
+                                               uint8_t* __restrict__ out) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wx0 = 8 * (warp & 3), wy0 = 4 * (warp >> 2);
+    const int frame = blockIdx.z;
+    const int W = cam.width, H = cam.height;
+    const FrameCtx* c = ctx + frame;
+    int tbx = blockIdx.x, tby = blockIdx.y;
+    {
+        const float bcx = __ldg(&c->cx), bcy = __ldg(&c->cy), brad = __ldg(&c->rad);
+        if (bounded) {
+            tbx += (int)floorf((bcx - brad) / (float)RW);
+            tby += (int)floorf((bcy - brad) / (float)RH);
+            if (tbx < 0 || tby < 0 || tbx * RW >= W || tby * RH >= H) return;
+        }
+        const float fx0 = (float)(tbx * RW), fy0 = (float)(tby * RH);
+        if (!(brad < 0.f || (fx0 <= bcx + brad && fx0 + (float)RW >= bcx - brad && fy0 <= bcy + brad && fy0 + (float)RH >= bcy - brad)))
+            return;
+    }
+    // the pixel bounds k_tri_setup found (one pixel of slack): blocks outside leave, patches outside skip the scan
+    const int qx0 = c->bx0 - 1, qx1 = c->bx1 + 1, qy0 = c->by0 - 1, qy1 = c->by1 + 1;
+    if (tbx * RW > qx1 || tbx * RW + RW < qx0 || tby * RH > qy1 || tby * RH + RH < qy0) return;
+    const bool live = !(tbx * RW + wx0 > qx1 || tbx * RW + wx0 + 8 < qx0 || tby * RH + wy0 > qy1 || tby * RH + wy0 + 4 < qy0);
+    const int px = tbx * RW + wx0 + (lane & 7), py = tby * RH + wy0 + (lane >> 3);
+
+    // background / ground of this pixel, as in k_background, keeping the depth of the ground hit
+    const float ex = __ldg(&c->eye[0]), ey = __ldg(&c->eye[1]), ez = __ldg(&c->eye[2]);
+    const float pxc = A((float)px, 0.5f), pyc = A((float)py, 0.5f);
+    const float txv = M(Sb(M(pxc, __ldg(&c->ihw)), 1.f), cam.tan_x), tyv = M(Sb(1.f, M(pyc, __ldg(&c->ihh))), cam.tan_y);
+    const float dx = A(A(cam.fwd[0], M(cam.up[0], tyv)), M(cam.right[0], txv));
+    const float dy = A(A(cam.fwd[1], M(cam.up[1], tyv)), M(cam.right[1], txv));
+    const float dz = A(A(cam.fwd[2], M(cam.up[2], tyv)), M(cam.right[2], txv));
+    uint32_t col = __ldg(&c->bg);
+    float best = 0.f;                                       // 1 / depth of the nearest surface so far (0: none)
+    int best_id = 0x7fffffff;
+    if (dz < 0.f && ez > 0.f) {
+        const float t = D(ez, -dz);
+        const float hx = A(ex, M(t, dx)), hy = A(ey, M(t, dy));
+        if (fabsf(hx) <= cam.ground_half && fabsf(hy) <= cam.ground_half) {
+            col = ((__float2int_rd(M(hx, cam.inv_checker)) + __float2int_rd(M(hy, cam.inv_checker))) & 1) ? __ldg(&c->gb) : __ldg(&c->ga);
+            best = D(1.f, t);
+        }
+    }
+
+    // pixel centres of the warp's patch span [wl + 1, wr - 1] x [wt + 1, wb - 1]: one pixel of slack around them
+    const float wl = (float)(tbx * RW + wx0) - 0.5f, wr = (float)(tbx * RW + wx0 + 8) + 0.5f;
+    const float wt = (float)(tby * RH + wy0) - 0.5f, wb = (float)(tby * RH + wy0 + 4) + 0.5f;
+    const float4* fb = bbs + (size_t)frame * n_tris;
+    const TriRec* fr = rec + (size_t)frame * n_tris;
+    for (int r0 = 0; live && r0 < n_tris; r0 += 32) {
+        bool hit = false;
+        if (r0 + lane < n_tris) {
+            const float4 bb = __ldg(fb + r0 + lane);
+            hit = !(bb.x > wr || bb.y < wl || bb.z > wb || bb.w < wt);
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, hit);
+        if (todo == 0u) continue;
+        // every lane with a hit fetches its own record (all loads in flight together); the warp then takes the records
+        // one by one out of the owners' registers, so no global-memory latency sits inside the serial walk
+        float4 ma = make_float4(0.f, 0.f, 0.f, 0.f), mb = ma, mc = ma;
+        if (hit) { const TriRec* q = fr + r0 + lane; ma = __ldg(&q->a); mb = __ldg(&q->b); mc = __ldg(&q->c); }
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const float x0 = __shfl_sync(0xffffffffu, ma.x, src), y0 = __shfl_sync(0xffffffffu, ma.y, src);
+            const float x1 = __shfl_sync(0xffffffffu, ma.z, src), y1 = __shfl_sync(0xffffffffu, ma.w, src);
+            const float x2 = __shfl_sync(0xffffffffu, mb.x, src), y2 = __shfl_sync(0xffffffffu, mb.y, src);
+            const float ia = __shfl_sync(0xffffffffu, mb.z, src), iz0 = __shfl_sync(0xffffffffu, mb.w, src);
+            const float iz1 = __shfl_sync(0xffffffffu, mc.x, src), iz2 = __shfl_sync(0xffffffffu, mc.y, src);
+            const float b0 = M(Sb(M(Sb(pxc, x1), Sb(y2, y1)), M(Sb(pyc, y1), Sb(x2, x1))), ia);
+            const float b1 = M(Sb(M(Sb(pxc, x2), Sb(y0, y2)), M(Sb(pyc, y2), Sb(x0, x2))), ia);
+            const float b2 = M(Sb(M(Sb(pxc, x0), Sb(y1, y0)), M(Sb(pyc, y0), Sb(x1, x0))), ia);
+            const bool inside = b0 >= 0.f && b1 >= 0.f && b2 >= 0.f;
+            if (__any_sync(0xffffffffu, inside)) {
+                const uint32_t pk = __shfl_sync(0xffffffffu, __float_as_uint(mc.z), src);
+                const int id = __shfl_sync(0xffffffffu, __float_as_int(mc.w), src);
+                const float izp = A(A(M(b0, iz0), M(b1, iz1)), M(b2, iz2));
+                if (inside && (izp > best || (izp == best && id < best_id))) { best = izp; best_id = id; col = pk; }
+            }
+        }
+    }
+    if (px < W && py < H) {
+        uint8_t* o = out + ((size_t)frame * H + py) * (size_t)W * 3 + (size_t)px * 3;
+        o[0] = (uint8_t)col; o[1] = (uint8_t)(col >> 8); o[2] = (uint8_t)(col >> 16);
     }
 }
 
@@ -273,6 +376,7 @@ void cf_raster_destroy(cf_raster* r) {
     cudaFree(r->tris);
     cudaFree(r->rgb);
     cudaFree(r->ctx);
+    cudaFree(r->rec);
     delete r;
 }
 
@@ -284,17 +388,52 @@ int cf_raster_render_dev(cf_raster* r, const cf_camera* cam, const float* poses_
     if (n_frames > 65535) return fail(CF_ERR_INVALID, "cf_raster_render_dev", "at most 65535 frames per call");
     if (n_frames == 0) return CF_OK;
     RCU(cudaSetDevice(r->device));
-    if (n_frames > r->ctx_frames) {                         // grows on demand (cudaFree waits for launches still using it)
+    // frames are processed in batches so that the per-(frame, triangle) records stay within ~256 MB
+    const size_t per_frame = (size_t)(r->n_tris > 0 ? r->n_tris : 1) * (sizeof(TriRec) + sizeof(float4));
+    int batch = (int)((size_t)256 << 20) / (int)(per_frame < ((size_t)256 << 20) ? per_frame : ((size_t)256 << 20));
+    if (batch < 1) batch = 1;
+    if (batch > n_frames) batch = n_frames;
+    if (batch > r->ctx_frames) {                            // grows on demand (cudaFree waits for launches still using it)
         cudaFree(r->ctx);
-        r->ctx = nullptr; r->ctx_frames = 0;
-        if (cudaMalloc(&r->ctx, (size_t)n_frames * sizeof(FrameCtx)) != cudaSuccess)
+        cudaFree(r->rec);
+        r->ctx = r->rec = nullptr; r->ctx_frames = r->rec_frames = 0;
+        if (cudaMalloc(&r->ctx, (size_t)batch * sizeof(FrameCtx)) != cudaSuccess || cudaMalloc(&r->rec, (size_t)batch * per_frame) != cudaSuccess)
             return fail(CF_ERR_ALLOC, "cf_raster_render_dev", "out of device memory");
-        r->ctx_frames = n_frames;
+        r->ctx_frames = r->rec_frames = batch;
     }
     FrameCtx* ctx = static_cast<FrameCtx*>(r->ctx);
-    k_frame_ctx<<<(n_frames + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*cam, r->radius, poses_dev, n_frames, ctx);
-    dim3 grid((cam->width + BW - 1) / BW, (cam->height + BH - 1) / BH, n_frames);
-    k_raster<<<grid, NT, 0, (cudaStream_t)stream>>>(r->tris, r->rgb, r->n_tris, *cam, ctx, rgb_dev);
+    TriRec* rec = static_cast<TriRec*>(r->rec);
+    float4* bbs = reinterpret_cast<float4*>(rec + (size_t)r->ctx_frames * (r->n_tris > 0 ? r->n_tris : 1));
+    cudaStream_t st = (cudaStream_t)stream;
+    // follow camera: the drone sits at the distance |eye_offset| on the view axis, so the size of its screen bound is
+    // known here (k_frame_ctx's formula with |x/z| = |y/z| = 0, plus slack for its float rounding)
+    const double dist = sqrt((double)cam->eye_offset[0] * cam->eye_offset[0] + (double)cam->eye_offset[1] * cam->eye_offset[1] +
+                             (double)cam->eye_offset[2] * cam->eye_offset[2]);
+    dim3 grid((cam->width + RW - 1) / RW, (cam->height + RH - 1) / RH, 1);
+    int bounded = 0;
+    if (cam->follow && dist - r->radius > cam->near_plane + 0.01) {
+        const double focal = fmax(0.5 * cam->width / cam->tan_x, 0.5 * cam->height / cam->tan_y);
+        const double rad = r->radius / (dist - r->radius) * 1.01 * focal + 3.0;
+        const unsigned nx = (unsigned)floor(2.0 * rad / RW) + 2, ny = (unsigned)floor(2.0 * rad / RH) + 2;
+        if (nx < grid.x || ny < grid.y) {
+            bounded = 1;
+            grid.x = nx < grid.x ? nx : grid.x;
+            grid.y = ny < grid.y ? ny : grid.y;
+        }
+    }
+    for (int f0 = 0; f0 < n_frames; f0 += batch) {
+        const int nf = n_frames - f0 < batch ? n_frames - f0 : batch;
+        uint8_t* o = rgb_dev + (size_t)f0 * cam->height * cam->width * 3;
+        k_frame_ctx<<<(nf + 127) / 128, 128, 0, st>>>(*cam, r->radius, poses_dev + 7 * (size_t)f0, nf, ctx);
+        dim3 gbg((cam->width + BW - 1) / BW, (cam->height + GH - 1) / GH, nf);
+        if (cam->right[2] == 0.f) k_background<true><<<gbg, NT, 0, st>>>(*cam, ctx, o);
+        else k_background<false><<<gbg, NT, 0, st>>>(*cam, ctx, o);
+        if (r->n_tris > 0) {
+            k_tri_setup<<<dim3((r->n_tris + NT - 1) / NT, nf), NT, 0, st>>>(r->tris, r->rgb, r->n_tris, *cam, ctx, rec, bbs);
+            grid.z = nf;
+            k_raster<<<grid, NT, 0, st>>>(r->n_tris, *cam, ctx, rec, bbs, bounded, o);
+        }
+    }
     RCU(cudaGetLastError());
     return CF_OK;
 }
