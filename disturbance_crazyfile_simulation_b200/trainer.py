@@ -136,9 +136,12 @@ class PPOTrainer:
                  use_reward_scaling: bool = True, use_linear_lr_decay: bool = True,
                  use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
                  target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
-                 gae_fn=None, logger=None, save_freq: int = 10):
+                 gae_fn=None, logger=None, save_freq: int = 10, val_freq: int = 0, val_kwargs: Optional[dict] = None):
         # logger: a run_logger.RunLogger (progress.csv / config.json / torch_save/model{epoch}.pt in the reference's
         # formats, loggers.py:205-513); save_freq as iwpg.py:45,302-304
+        # val_freq > 0: validate() every val_freq epochs (iwpg.py:66,297-301; the reference's default is 50); val_kwargs are
+        # passed to validate() (num_evaluations, camera, frame_stride, ...)
+        self.val_freq, self.val_kwargs, self._val_env = int(val_freq), dict(val_kwargs or {}), None
         self.logger, self.save_freq, self.seed, self._t_start = logger, int(save_freq), seed, time.time()
         if gae_fn is None:                                   # the fused CUDA kernel; tests of the host logic inject a stand-in
             from .gae import gae as gae_fn
@@ -296,7 +299,72 @@ class PPOTrainer:
                     FPS=self.T * self.N * self.world / (t2 - t0))
         if self.logger is not None:
             self._log_epoch(info, current_lr)
+        if self.val_freq > 0 and self.epoch % self.val_freq == 0:
+            info['validation'] = self.validate(**self.val_kwargs)
         return info
+
+    # ------------------------------------------------------------------ validation (iwpg.py:512-568)
+    @torch.no_grad()
+    def validate(self, num_evaluations: int = 8, capture: bool = True, camera=None, frame_stride: int = 1,
+                 gif_duration_ms: int = 500, max_steps: Optional[int] = None):
+        """``IWPGAlgorithm.validate`` / ``val_once``: ``num_evaluations`` episodes of the deterministic policy, one row each
+        in ``validation_results.csv`` and, with ``capture``, one ``{epoch}-{episode}-{level}.gif`` each under
+        ``validation_gifs/`` holding a ``capture_image()`` frame per control step.  The reference runs the episodes one after
+        the other on its single env; here they run side by side on a ``num_evaluations``-env twin of the training env
+        (same id, same knobs, same HJ tables, no auto-reset) and every step's frames come from one rasteriser launch.
+        ``camera`` (raster.make_camera) sets the frame size; default is the reference's 1920x1080.  Rank 0 only, no
+        collective.  The per-step penalty terms the reference writes to ``penalty_data.csv`` are not tracked by the step
+        kernel; that file keeps its header."""
+        if self.rank != 0:
+            return None
+        env, k = self.env, int(num_evaluations)
+        if self._val_env is None or self._val_env.num_envs != k:
+            from .vec_env import CrazyFlieVecEnv
+            kw = dict(getattr(env, '_kwargs', {}))
+            kw['auto_reset'] = 0
+            self._val_env = CrazyFlieVecEnv(env.id, num_envs=k, device=env.device_index, seed=self.seed + 7919,
+                                            env_id_base=1 << 40, share_tables_with=env, **kw)
+        venv = self._val_env
+        was_training = self.ac.training
+        self.ac.eval()
+        o = venv.reset()
+        levels = venv.disturbance_level
+        alive = torch.ones(k, dtype=torch.bool, device=self.dev)
+        ret = torch.zeros(k, device=self.dev)
+        cost = torch.zeros(k, device=self.dev)
+        length = torch.zeros(k, dtype=torch.int32, device=self.dev)
+        frames = [[] for _ in range(k)]
+        limit = int(max_steps or venv._max_episode_steps)
+        for t in range(limit):
+            if capture and t % frame_stride == 0:
+                img = venv.capture_images(None, camera=camera).cpu().numpy()        # [k, H, W, 3], one launch
+                live = alive.cpu().numpy()
+                for i in range(k):
+                    if live[i]:
+                        frames[i].append(img[i])
+            a, _, _ = self.ac.step(o, deterministic=True)
+            o, r, d, info = venv.step(a)
+            ret += torch.where(alive, r, torch.zeros_like(r))
+            cost += torch.where(alive, info['cost'], torch.zeros_like(r))
+            length += alive.to(torch.int32)
+            alive &= ~d.bool()
+            if not bool(alive.any()):
+                break
+        self.ac.train(was_training)
+        out = dict(epoch=self.epoch, disturbance_level=[float(x) for x in levels], steps=[float(x) for x in length.cpu()],
+                   returns=[float(x) for x in ret.cpu()], costs=[float(x) for x in cost.cpu()], gifs=[])
+        if self.logger is not None:
+            self.logger.log_validation([self.epoch] * k, out['disturbance_level'], out['steps'], out['returns'], out['costs'])
+            if capture:
+                from PIL import Image
+                for i in range(k):
+                    if not frames[i]:
+                        continue
+                    ims = [Image.fromarray(f) for f in frames[i]]
+                    path = f"{self.logger.validation_gifs}/{self.epoch}-{i}-{out['disturbance_level'][i]}.gif"
+                    ims[0].save(path, save_all=True, append_images=ims[1:], duration=gif_duration_ms, loop=0)
+                    out['gifs'].append(path)
+        return out
 
     def _log_epoch(self, info: dict, current_lr: float) -> None:
         """One progress.csv row with the column names of IWPGAlgorithm.log (iwpg.py:309-348) for the quantities the

@@ -95,6 +95,7 @@ class CrazyFlieVecEnv:
             ftype = dict(abi.CfConfig._fields_)[field]
             setattr(cfg, field, int(v) if ftype is C.c_int32 else float(v))
         self.cfg = cfg
+        self._kwargs = dict(kwargs)                      # so that a validation env can be built with the same knobs
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             abi.check(L.cf_create(C.byref(cfg), self.num_envs, self.device_index, int(seed) & (2 ** 64 - 1),

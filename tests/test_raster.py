@@ -163,3 +163,38 @@ def test_env_capture_image_follows_the_drone():
     with pytest.raises(NotImplementedError):
         env.render('human')
     env.close()
+
+
+@pytest.mark.gpu
+def test_trainer_validation_writes_rows_and_gifs(tmp_path):
+    """IWPGAlgorithm.validate / val_once (iwpg.py:512-568): deterministic-policy episodes on a twin env, one row each in
+    validation_results.csv, one GIF each with a capture_image() frame per control step."""
+    import csv
+    from PIL import Image
+    from disturbance_crazyfile_simulation_b200 import make
+    from disturbance_crazyfile_simulation_b200.run_logger import RunLogger
+    from disturbance_crazyfile_simulation_b200.trainer import PPOTrainer
+    env = make('DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', num_envs=256, seed=3, return_terminal_obs=True)
+    lg = RunLogger(str(tmp_path))
+    cam = raster.make_camera(128, 72)
+    t = PPOTrainer(env, rollout_len=8, epochs=4, train_pi_iterations=2, train_v_iterations=1, num_mini_batches=2, seed=0, logger=lg,
+                   val_freq=1, val_kwargs=dict(num_evaluations=3, camera=cam, max_steps=40))
+    info = t.learn_one_epoch()
+    val = info['validation']
+    assert val['epoch'] == 1 and len(val['returns']) == 3 and all(1 <= s <= 40 for s in val['steps'])
+    assert all(r < 0 for r in val['returns']) and len(val['gifs']) == 3
+    with open(tmp_path / 'validation_results.csv') as f:
+        rows = list(csv.reader(f))
+    assert rows[0] == ['Training_Epoch', 'disturbance_level', 'Steps', 'Returns', 'Costs'] and len(rows) == 4
+    for i, path in enumerate(val['gifs']):
+        assert path.endswith(f"1-{i}-{val['disturbance_level'][i]}.gif")
+        with Image.open(path) as im:
+            assert im.size == (128, 72) and im.n_frames == int(val['steps'][i])
+        assert float(rows[1 + i][2]) == val['steps'][i] and abs(float(rows[1 + i][3]) - val['returns'][i]) < 1e-4
+    # the twin env does not disturb the training env: a second epoch still runs, and a second validation appends rows
+    info = t.learn_one_epoch()
+    assert info['validation']['epoch'] == 2
+    lg.close()
+    with open(tmp_path / 'validation_results.csv') as f:
+        assert len(list(csv.reader(f))) == 7
+    env.close()
