@@ -37,8 +37,13 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
 #ifndef CF_PHILOX_ROUNDS
 #define CF_PHILOX_ROUNDS 10             /* tools/ only: instruction-count sensitivity probes build with fewer rounds */
 #endif
+#define CF_PRAGMA_(x) _Pragma(#x)
+#define CF_UNROLL_N_(n) CF_PRAGMA_(unroll n)
+#ifndef CF_PHILOX_UNROLL
+#define CF_PHILOX_UNROLL CF_PHILOX_ROUNDS   /* tools/ only: smaller values trade straight-line rounds for code size */
+#endif
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, const DevCfg& cfg) {
-#pragma unroll
+    CF_UNROLL_N_(CF_PHILOX_UNROLL)
     for (int r = 0; r < CF_PHILOX_ROUNDS; ++r) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
         uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
@@ -768,6 +773,9 @@ struct StepDraws {
 };
 // PART 0: blocks 0..5 (+ the random-box uniforms); PART 1: blocks 6..10 and the observation uniforms.  The step
 // kernel runs part 0 while the tile is in flight and part 1 behind the HJ table gather.
+#ifndef CF_RNG_UNROLL
+#define CF_RNG_UNROLL 1
+#endif
 template <bool NOISE, int PART>
 __device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCfg& cfg, float* scratch, StepDraws& sd) {
     if (PART == 0) {
@@ -779,7 +787,10 @@ __device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCf
         else sd.r1 = sd.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (NOISE) {
-#pragma unroll
+        // not unrolled: each Philox + Box-Muller body is ~2.2 KB of code and the step's executed path already overflows the
+        // 32 KB instruction cache (ncu: 39 % of the stall samples are no_instruction); one body for the seven blocks is
+        // 14 KB less code and measured +2 % (A/B on one box, -DCF_RNG_UNROLL=... rebuilds the unrolled form)
+        CF_UNROLL_N_(CF_RNG_UNROLL)
         for (int b = (PART == 0 ? 4 : 6); b < (PART == 0 ? 6 : 11); ++b) {
             float4 v = dw.z(cfg, b);
             float* p = scratch + (4 * (b - 4)) * 32;
