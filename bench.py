@@ -32,11 +32,20 @@ HOVER = 2.0 / 1.8 - 1.0
 # 216 B out, DR params 56 B in, action 16 B in, obs 136 B + reward 4 B + done 1 B + cost 4 B out,
 # HJ packed sign table 1 B gathered.
 BYTES_PER_ENV_STEP = 216 + 216 + 56 + 16 + 136 + 4 + 1 + 4 + 1
-# dram__bytes_read.sum + dram__bytes_write.sum per k_step launch (bytes), mean of the 3 launches of the committed
-# ncu --set full capture profiles/r1_v5_ncu_summary.md (caches flushed per replay): 42.36 MB read (this shard's state +
-# actions + parameters, and the next shard's 21 MB prefetched into L2) + 0.05 MB written during the kernel; the
-# ~25 MB of new state and I/O rows stay dirty in the 126 MB L2 and are written back while later launches run.
-TRAFFIC_NCU = 42.41e6
+
+
+def ncu_kstep_metrics():
+    """dram bytes and warp-instructions per k_step launch from the newest committed ncu --set full capture
+    (profiles/*kstep_ncu_metrics.json, written by tools/ncu_summary.py --json from the .ncu-rep): a measurement of a
+    profiled run of this same command, quoted with its file name - not a measurement of THIS run."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', '*kstep_ncu_metrics.json')))
+    if not files:
+        return None
+    with open(files[-1]) as f:
+        m = json.load(f)
+    m['file'] = os.path.relpath(files[-1], ROOT)
+    return m
 
 
 try:
@@ -54,7 +63,7 @@ def parse():
     ap.add_argument('--envs', type=int, default=65536, help='envs per GPU per step')
     ap.add_argument('--shards', type=int, default=8, help='independent env shards per GPU (L2 eviction)')
     ap.add_argument('--kfuse', type=int, default=32, help='control steps per launch in the fused side measurement')
-    ap.add_argument('--e2e-steps', type=int, default=100)
+    ap.add_argument('--e2e-steps', type=int, default=200)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--graph-passes', type=int, default=4, help='round-robin passes over the shards captured in the CUDA graph')
@@ -73,6 +82,8 @@ def parse():
                          '(episodes run to the 500-step limit)')
     ap.add_argument('--no-bind', action='store_true', help='do not pin the process to the CPUs local to its GPU (NVML affinity)')
     ap.add_argument('--no-graph', action='store_true', help='launch every step directly instead of replaying a CUDA graph')
+    ap.add_argument('--repeats', type=int, default=0,
+                    help='timed regions of exactly --steps launches each (median reported); 0 = as many as make the regions last ~60 ms')
     return ap.parse_args()
 
 
@@ -124,14 +135,17 @@ def measured_peaks():
     return 6650.0, 'fallback 6.65 TB/s of B200_PROFILING.md (of fallback)'
 
 
-def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float, env_id: str = ENV_ID):
+def cpu_reference_run(envs: int, steps: int, warmup: int, seconds: float, env_id: str = ENV_ID, env_kw=None):
     """The reference algorithm on the host cores: oracle-B (float64 C restatement of the reference's
-    Python + restated Bullet step, OpenMP over envs) on a bounded sample of the same workload."""
+    Python + restated Bullet step, OpenMP over envs) on a bounded sample of the same workload.
+    Nothing of the product package is imported or loaded here: config defaults and the synthetic HJ table come from
+    oracle/ (cfo_config_default, cf_oracle.synthetic_table)."""
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import cf_oracle as co
-    from disturbance_crazyfile_simulation_b200 import abi, hj_tables
-    cfg = abi.config_default(env_id)
-    V = hj_tables.synthetic_table(1.5, 15)
+    cfg = co.config_default(env_id)
+    for k, v in (env_kw or {}).items():
+        setattr(cfg, k, v)
+    V = co.synthetic_table(1.5, 15)
     for li in range(1, 21):          # one table shared by all levels: the lookup cost does not depend on its values
         co.set_table(li, V)
     try:                                                     # all host cores again if the process was bound to the GPU's node
@@ -160,20 +174,31 @@ def main_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    envs = 16384
+    wl = WORKLOADS[args.workload if args.workload in WORKLOADS else 'hover_hj']
+    env_id = wl['env_id']
+    envs = wl['envs'] if args.envs == 65536 else args.envs           # the product arm's envs per GPU per step
+    env_kw = {'use_ground_effect': args.ground_effect} if args.workload == 'initial' else {}
     steps = max(1, min(args.steps, 2000))
-    value, cores, done_steps, dt = cpu_reference_run(envs, steps, min(args.warmup, 5), 60.0)
-    sample = f'{envs} envs x {done_steps} control steps of {ENV_ID} (noise, DR, auto-reset on), synthetic HJ table'
+    warm = min(args.warmup, 5)
+    value, cores, done_steps, dt = cpu_reference_run(envs, steps, warm, 120.0, env_id, env_kw)
+    sample = (f'{envs} envs x {done_steps} control steps of {env_id} (noise, DR, auto-reset on), synthetic HJ table; every step is a '
+              f'full {envs}-env step of the product arm\'s workload')
+    loaded = sorted({ln.split()[-1] for ln in open('/proc/self/maps') if ln.rstrip().endswith('.so') and ROOT in ln}) \
+        if os.path.exists('/proc/self/maps') else []
     line = {
         'impl': 'reference', 'metric': 'env-steps/sec (HJ-adversary hover)', 'value': value, 'unit': 'env-steps/s',
-        'n_gpus': args.gpus, 'steps': done_steps, 'warmup': min(args.warmup, 5), 'ms_per_step': 1e3 * dt / done_steps,
+        'n_gpus': args.gpus, 'steps': done_steps, 'warmup': warm, 'ms_per_step': 1e3 * dt / done_steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': f'{ENV_ID}, bounded CPU sample of {envs} envs per step', 'envs_per_step': envs},
+        'config': {'workload': f'{env_id}, {envs} envs/GPU per step ({wl["tag"]}); sensor noise, 10% domain randomisation, '
+                               + ('Boltzmann HJ level' if env_id == ENV_ID else f'HJ level 1.5, ground effect {args.ground_effect}')
+                               + ', auto-reset, TimeLimit 500 all on - the product arm\'s config, stepped on the host cores',
+                   'envs_per_gpu_per_step': envs},
         'cpu_baseline': {'value': value, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                          'note': 'the reference itself (pure Python + PyBullet 3.21) cannot be installed here; this is its '
-                                 'algorithm restated in C (oracle-B), which is far faster than the reference\'s own '
+                                 'algorithm restated in C (oracle-B, float64, OpenMP over envs), far faster than the reference\'s own '
                                  '~1.2e3 (no adversary) / ~1.5e2 (HJ) steps/s per process (BASELINE.md)'},
         'e2e': {'value': value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'native_so_in_repo_loaded': [os.path.relpath(x, ROOT) for x in loaded],
     }
     print(json.dumps(line))
 
@@ -271,45 +296,73 @@ def main_ours(args):
         for st in side_streams:
             main.wait_stream(st)
 
-    # ---- warm-up (direct launches), then one CUDA graph of S launches (one control step of every shard) --
+    # ---- warm-up (direct launches); then every timed launch is replayed from CUDA graphs ------------------
     run(W)
     torch.cuda.synchronize()
-    graph = None
-    if not args.no_graph:
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            run(S * GP, offset=W)
-        graph.replay()                                   # untimed warm-up replay
-        torch.cuda.synchronize()
+    CH = S * GP                                          # launches per graph chunk
+    graphs = {}                                          # (launches, first shard) -> captured graph
 
-    def run_timed(k_steps):
-        """exactly k_steps control steps: whole-graph replays (S steps each) + direct launches for the rest"""
-        if graph is None:
-            run(k_steps, offset=W)
+    def graph_for(k_steps, offset):
+        key = (k_steps, offset % S)
+        if key not in graphs:
+            g_ = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_):
+                run(k_steps, offset=offset % S)
+            g_.replay()                                  # untimed warm-up replay (one more control step of those shards)
+            graphs[key] = g_
+        return graphs[key]
+
+    def plan(k_steps, offset):
+        """[(launches, first shard)]: exactly k_steps control steps continuing the round-robin at `offset`, in chunks of
+        at most CH launches; a shard always steps on the same stream, so any run of the round-robin is a legal graph."""
+        out, o, left = [], offset, k_steps
+        while left > 0:
+            c = min(CH, left)
+            out.append((c, o % S))
+            o += c; left -= c
+        return out
+
+    def run_timed(k_steps, offset):
+        """exactly k_steps control steps, every launch from a CUDA graph (or direct with --no-graph)"""
+        if args.no_graph:
+            run(k_steps, offset=offset)
             return
-        for _ in range(k_steps // (S * GP)):
-            graph.replay()
-        run(k_steps % (S * GP), offset=W)
+        for c, o in plan(k_steps, offset):
+            graphs[(c, o)].replay()
 
     # per-launch device time of the step kernel with CUDA events on the launching stream (direct launches)
     for e in shards:
         e.kernel_timing(True, reset=True)
-    run(min(K, 200), offset=W)
+    run(min(max(K, 64), 200), offset=W)
     torch.cuda.synchronize()
     kt = [e.kernel_timing(False) for e in shards]
     kern_ms_events = sum(m * c for m, c in kt) / max(1, sum(c for _, c in kt))
 
-    # ---- the timed region: exactly K steps between barrier + synchronize -----------------------------
+    # ---- the timed region: exactly K steps between barrier + synchronize, repeated R times --------------------
+    # A region of K = 20 launches lasts ~0.3 ms, shorter than the jitter of its own bracketing; the region is therefore
+    # repeated R times back to back (R chosen so that the R regions last >= ~60 ms), each region timed with its own
+    # CUDA-event pair on the launching stream, and the MEDIAN region is reported (`repeats`: R).  The round-robin over
+    # the shards continues across regions, so every launch of every region finds its shard evicted from the L2.
+    est_ms = max(kern_ms_events, 1e-3) * K
+    R = 1 if args.repeats == 1 else (args.repeats if args.repeats > 0 else int(min(400, max(3, round(60.0 / est_ms)))))
+    if not args.no_graph:
+        for r in range(R):
+            for c, o in plan(K, W + r * K):
+                graph_for(c, o)
+        torch.cuda.synchronize()
     sampler = ClockSampler(local) if rank == 0 else None
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(R + 1)]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t0 = time.time()
-    ev0.record()
-    run_timed(K)
-    ev1.record()
+    evs[0].record()
+    for r in range(R):
+        run_timed(K, W + r * K)
+        evs[r + 1].record()
     barrier()
     t1 = time.time()
-    ms = ev0.elapsed_time(ev1)
+    regions = [evs[r].elapsed_time(evs[r + 1]) for r in range(R)]
+    ms = statistics.median(regions)
     launches = K * (2 if PD else 1)                      # one k_step launch per control step (graph nodes included) [+ k_pd_actions]
     clocks = sampler.stop(t0, t1) if sampler else None
     kern_ms = ms / K                                     # launch-to-launch time of the dominant kernel inside the timed region
@@ -409,7 +462,7 @@ def main_ours(args):
                 pinned((n,), np.float32)]
         sets.append([b for b, _ in bufs]); ptrs += [q for _, q in bufs]
         sets[-1][0][:] = acts[0].cpu().numpy()
-    ke = max(3, min(args.e2e_steps, K))
+    ke = max(3 * D, args.e2e_steps)                    # its own step count: a region of K = 20 steps would be 7 pipeline fills
 
     def e2e_loop(count):
         for i in range(count):
@@ -430,14 +483,28 @@ def main_ours(args):
     e2e_value = n * ke * world / float(t_e.item())
     for q in ptrs:
         L.cf_host_free(q)
+    e2e_h2d, e2e_d2h = n * 16, n * (4 * od + 4 + 1 + 4)
+    e2e_api = (f'cf_step_host_async + cf_host_sync (C ABI, pinned host buffers, {D} steps in flight over the shards; '
+               'uploads and downloads inside the timed region)')
 
     if rank == 0:
         peak, peak_src = measured_peaks()
         achieved = BYTES_PER_ENV_STEP * n / (kern_ms * 1e-3) / 1e9
+        achieved_launch = BYTES_PER_ENV_STEP * n / (kern_ms_events * 1e-3) / 1e9
+        nm = ncu_kstep_metrics()
+        sm_hz = 1e6 * float((clocks or {}).get('sm_mhz') or 1965.0)
+        issue_floor_ms = (nm['inst_executed_per_launch'] * (n / nm['envs_per_launch']) / (148 * 4 * sm_hz) * 1e3) if nm else None
+        if args.no_graph:
+            step_mode = 'one kernel launch per control step, launched directly'
+        else:
+            chunks = sorted({c for c, _ in plan(K, W)}, reverse=True)
+            step_mode = (f'one kernel launch per control step; all {K} launches of a timed region are replayed from CUDA graphs '
+                         f'(chunks of {" + ".join(str(c) for c in chunks)} launches, round-robin over the {S} shards continued across regions)')
         line = {
             'metric': 'env-steps/sec (HJ-adversary hover)', 'value': value, 'unit': 'env-steps/s', 'n_gpus': world,
             'steps': K, 'warmup': W, 'ms_per_step': ms_max / K, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'repeats': R, 'region_ms': {'median': ms, 'min': min(regions), 'max': max(regions), 'first': regions[0]},
             'config': {'workload': f'{ENV_ID}, {n} envs/GPU per step ({wl["tag"]}); sensor noise, 10% domain '
                                    'randomisation, ' + ('Boltzmann HJ level' if args.workload == 'hover_hj' else f'HJ level 1.5, ground effect {args.ground_effect}') + ', in-kernel auto-reset, TimeLimit 500 all on',
                        'envs_per_gpu_per_step': n, 'shards_per_gpu': S,
@@ -446,28 +513,36 @@ def main_ours(args):
                                    'pd': 'on-device attitude-rate PD on the noisy observation (cf_pd_actions_dev, one extra kernel per step)'}[args.actions],
                        'hj_tables': '20 synthetic float32 (15,)*6 tables (real blobs missing from the reference checkout), '
                                     'packed 2-bit sign tables in HBM/L2',
-                       'step_mode': 'one kernel launch per control step' + ('' if args.no_graph else f', launches replayed from a CUDA graph of {S * GP} ({GP} passes over the {S} shards)')
-                                    + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else ''),
+                       'step_mode': step_mode + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else ''),
+                       'timing': f'{R} regions of exactly {K} launches each, back to back between one barrier + synchronize pair, each region '
+                                 'timed by its own CUDA-event pair; value = median region, max over ranks',
                        'shard_pipelining': ('off' if args.no_prefetch or S == 1 else
                                             'each step kernel issues cp.async.bulk.prefetch.L2 for the state + actions of the shard stepped next '
                                             '(cf_set_prefetch_next); every byte still comes from HBM once per step')},
             'clocks': clocks, 'gpu_launches': int(launches),
-            'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': n * 16,
-                    'd2h_bytes_per_step': n * (4 * od + 4 + 1 + 4), 'steps': ke,
-                    'api': f'cf_step_host_async + cf_host_sync (C ABI, pinned host buffers, {D} steps in flight over the shards; '
-                           'uploads and downloads inside the timed region)',
-                    'host_binding_rank0': host_binding},
+            'e2e': {'value': e2e_value, 'unit': 'env-steps/s', 'h2d_bytes_per_step': e2e_h2d,
+                    'd2h_bytes_per_step': e2e_d2h, 'steps': ke,
+                    'api': e2e_api, 'host_binding_rank0': host_binding},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': TRAFFIC_NCU, 'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
+                         'frac_per_launch': achieved_launch / peak,
+                         'issue_frac': (issue_floor_ms / kern_ms) if issue_floor_ms else None,
+                         'traffic': (nm['dram_bytes_per_launch'] if nm else None),
+                         'traffic_source': (nm['file'] if nm else None),
+                         'kernel': 'cf::k_step<true, CF_HJ_SIGN_TABLE>', 'avg_kernel_ms': kern_ms,
                          'avg_kernel_ms_events_per_launch': kern_ms_events,
+                         'issue_floor_ms': issue_floor_ms,
+                         'warp_inst_per_launch': (nm['inst_executed_per_launch'] * (n / nm['envs_per_launch']) if nm else None),
                          'bytes_per_env_step': BYTES_PER_ENV_STEP, 'peak_source': peak_src,
-                         'note': 'avg_kernel_ms = CUDA-event time of the timed region / launches in it (launch gaps included); '
-                                 'avg_kernel_ms_events_per_launch = CUDA events around each direct launch on the launching stream; '
-                                 'traffic = dram bytes per launch from the committed ncu --set full capture (profiles/)'},
+                         'note': 'frac = sustained: algorithmic bytes per launch / (median timed region / launches in it), the launches of the '
+                                 'two streams overlap; frac_per_launch = the same bytes / the un-overlapped duration of one launch (CUDA events '
+                                 'around direct launches on the launching stream); issue_frac = the second ceiling: warp-instructions per '
+                                 'launch (ncu smsp__inst_executed.sum of the committed capture) / (148 SMs x 4 schedulers x the SM clock '
+                                 'sampled during this run) / avg_kernel_ms; traffic = dram bytes per launch of that same committed ncu '
+                                 '--set full capture (traffic_source), not of this run'},
             'side': side,
         }
         if not args.no_cpu_baseline:
-            v, cores, steps_done, dt = cpu_reference_run(8192, 10000, 2, args.cpu_seconds, ENV_ID)
+            v, cores, steps_done, dt = cpu_reference_run(8192, 10000, 2, args.cpu_seconds, ENV_ID, env_kw)
             line['cpu_baseline'] = {'value': v, 'unit': 'env-steps/s', 'cores': cores, 'kind': 'port',
                                     'sample': f'8192 envs x {steps_done} control steps of the same workload ({dt:.1f} s), '
                                               'oracle-B float64 C restatement, OpenMP'}

@@ -827,3 +827,51 @@ void cfo_hj_signs_all(const float* V, uint8_t* out) {
         out[b] = (uint8_t)v;
     }
 }
+
+/* ------------------------------------------------------------------ constructor defaults */
+/* The kwargs defaults of the registered env ids (phoenix_drone_simulation/__init__.py:8-109; constructors and
+ * compute_done overrides in envs/hover_free.py:18-39,303-326,449-461 and envs/hover.py:18-40,565-590,1290-1317;
+ * DroneBaseEnv defaults envs/base.py:26-47), so that bench.py's reference arm needs nothing from the product
+ * package.  tests/test_oracle_golden.py checks it field by field against cf_config_default of the CUDA library. */
+typedef struct { const char* id; int reward, dstb; double level, rp_deg, rate_deg, init_angle, rate_lim_deg; } cfo_id_defaults;
+static const cfo_id_defaults CFO_IDS[] = {
+    {"DroneHoverBulletFreeEnvWithoutAdversary-v0", CF_REWARD_FREE, CF_DSTB_NONE, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletFreeEnvWithAdversary-v0", CF_REWARD_FREE, CF_DSTB_HJ_FIXED, 1.5, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletFreeEnvWithRandomHJAdversary-v0", CF_REWARD_FREE, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnv-v0", CF_REWARD_TARGET, CF_DSTB_NONE, 0.0, 60, 300, PI / 6, 200},
+    {"DroneHoverBulletEnvWithoutAdversary-v0", CF_REWARD_TARGET, CF_DSTB_NONE, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnvWithAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_FIXED, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnvWithRandomHJAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnvWithCurriculumHJAdversary-v0", CF_REWARD_TARGET, CF_DSTB_HJ_BOLTZMANN, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnvWithRandomAdversary-v0", CF_REWARD_TARGET, CF_DSTB_RANDOM_BOX, 0.0, 75, 1000, PI / 6, 200},
+    {"DroneHoverBulletEnvWithAdversaryInitial-v0", CF_REWARD_TARGET, CF_DSTB_HJ_FIXED, 1.5, 75, 1000, PI / 4, 300},
+};
+int cfo_config_default(const char* env_id, cf_config* c) {
+    const cfo_id_defaults* d = NULL;
+    for (size_t k = 0; k < sizeof(CFO_IDS) / sizeof(CFO_IDS[0]); ++k)
+        if (strcmp(CFO_IDS[k].id, env_id) == 0) d = &CFO_IDS[k];
+    if (!d) return -1;
+    memset(c, 0, sizeof(*c));
+    c->abi_version = CF_ABI_VERSION;
+    c->reward_kind = d->reward; c->disturbance_kind = d->dstb;
+    c->observation_noise = 1; c->enable_reset_distribution = 1;
+    c->aggregate_phy_steps = 2; c->max_episode_steps = 500;
+    c->gyroscopic = 1; c->use_ground_effect = 0;
+    c->hj_mode = CF_HJ_SIGN_TABLE; c->rng_mode = CF_RNG_PHILOX; c->auto_reset = 1;
+    c->domain_randomization = 0.10; c->disturbance_level = d->level;
+    if (d->reward == CF_REWARD_FREE) {
+        c->penalty_action = 0.0; c->penalty_angle = 1.0; c->penalty_spin = 1.0;
+        c->penalty_terminal = 1000.0; c->penalty_velocity = 1.0; c->penalty_z = 0.0;
+    } else {
+        c->penalty_action = 1e-4; c->penalty_angle = 0.0; c->penalty_spin = 1e-4;
+        c->penalty_terminal = 1000.0; c->penalty_velocity = 0.0; c->penalty_z = 0.0;
+    }
+    c->done_roll_pitch_rad = deg2rad(d->rp_deg); c->done_rate_deg = d->rate_deg;
+    c->init_pos_lim = 0.25; c->init_angle = d->init_angle; c->init_yaw = 2.0 * PI;
+    c->init_vel_lim = 0.1; c->init_rate_lim = deg2rad(d->rate_lim_deg); c->init_yaw_rate_lim = deg2rad(20.0);
+    c->cost_rate_limit = deg2rad(d->rate_lim_deg);
+    c->sim_time_step = 1.0 / 200.0; c->motor_time_constant = 0.080;
+    c->motor_thrust_noise = 0.05; c->latency = 0.015;
+    c->linear_damping = 0.04; c->angular_damping = 0.04;
+    return 0;
+}

@@ -18,8 +18,40 @@ if _ROOT not in sys.path:
 if _HERE not in sys.path:
     sys.path.insert(0, _HERE)
 
-from disturbance_crazyfile_simulation_b200.abi import (  # noqa: E402  (struct layout only, no GPU code)
-    CF_RESET_NORMALS, CF_RESET_UNIFORMS, CF_STATE_WORDS, CF_STEP_NORMALS, CF_STEP_UNIFORMS, CfConfig)
+# Mirror of `cf_config` and the draw / record sizes of include/cf_abi.h.  Defined here (not imported from the product
+# package) so that bench.py's reference arm runs without loading anything of the product; tests/test_abi_cpu.py checks
+# that the two struct layouts are the same.
+CF_STEP_NORMALS, CF_STEP_UNIFORMS, CF_RESET_NORMALS, CF_RESET_UNIFORMS = 44, 8, 48, 42
+CF_STATE_WORDS = 76
+
+
+class CfConfig(C.Structure):
+    _fields_ = (
+        [(n, C.c_int32) for n in (
+            'abi_version', 'reward_kind', 'disturbance_kind', 'observation_noise',
+            'enable_reset_distribution', 'aggregate_phy_steps', 'max_episode_steps', 'gyroscopic',
+            'use_ground_effect', 'hj_mode', 'rng_mode', 'auto_reset')]
+        + [(n, C.c_double) for n in (
+            'domain_randomization', 'disturbance_level',
+            'penalty_action', 'penalty_angle', 'penalty_spin', 'penalty_terminal', 'penalty_velocity', 'penalty_z',
+            'done_roll_pitch_rad', 'done_rate_deg',
+            'init_pos_lim', 'init_angle', 'init_yaw', 'init_vel_lim', 'init_rate_lim', 'init_yaw_rate_lim',
+            'cost_rate_limit', 'sim_time_step', 'motor_time_constant', 'motor_thrust_noise', 'latency',
+            'linear_damping', 'angular_damping')])
+
+    def copy(self):
+        out = CfConfig()
+        C.memmove(C.byref(out), C.byref(self), C.sizeof(CfConfig))
+        return out
+
+
+def _cfg_copy(cfg):
+    """a private copy of a cf_config given as this module's CfConfig or the product binding's (same layout)"""
+    assert C.sizeof(cfg) == C.sizeof(CfConfig), 'cf_config layout mismatch'
+    out = CfConfig()
+    C.memmove(C.byref(out), C.byref(cfg), C.sizeof(CfConfig))
+    return out
+
 
 import build as _build  # noqa: E402  (oracle/build.py)
 
@@ -35,10 +67,10 @@ def lib():
         L.cfo_sizeof_env.restype = C.c_int
         L.cfo_num_threads.restype = C.c_int
         L.cfo_obs_dim.restype = C.c_int
-        L.cfo_obs_dim.argtypes = [C.POINTER(CfConfig)]
-        L.cfo_init_batch.argtypes = [_P, C.c_int, C.POINTER(CfConfig), C.c_uint64, C.c_int64]
-        L.cfo_reset_batch.argtypes = [_P, C.c_int, C.POINTER(CfConfig), _P, _P, _P, _P]
-        L.cfo_step_batch.argtypes = [_P, C.c_int, C.POINTER(CfConfig)] + [_P] * 11
+        L.cfo_obs_dim.argtypes = [_P]
+        L.cfo_init_batch.argtypes = [_P, C.c_int, _P, C.c_uint64, C.c_int64]
+        L.cfo_reset_batch.argtypes = [_P, C.c_int, _P, _P, _P, _P, _P]
+        L.cfo_step_batch.argtypes = [_P, C.c_int, _P] + [_P] * 11
         L.cfo_get_state_batch.argtypes = [_P, C.c_int, _P]
         L.cfo_set_state_batch.argtypes = [_P, C.c_int, _P]
         L.cfo_set_table.argtypes = [C.c_int, _P]
@@ -52,6 +84,8 @@ def lib():
         L.cfo_boltzmann_cdf.argtypes = [_P]
         L.cfo_gae.argtypes = [_P, _P, _P, _P, _P, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, _P, _P, _P]
         L.cfo_set_motor_A.argtypes = [_P, _P]
+        L.cfo_config_default.restype = C.c_int
+        L.cfo_config_default.argtypes = [C.c_char_p, _P]
         _lib = L
     return _lib
 
@@ -77,6 +111,30 @@ def set_table(level_idx: int, V: np.ndarray) -> None:
     assert V.shape == (15,) * 6
     _tables[level_idx] = V
     lib().cfo_set_table(level_idx, _p(V))
+
+
+def config_default(env_id: str) -> CfConfig:
+    """Constructor defaults of a registered env id (cfo_config_default), as the oracle's own CfConfig."""
+    cfg = CfConfig()
+    if lib().cfo_config_default(env_id.encode(), C.byref(cfg)) != 0:
+        raise KeyError(env_id)
+    return cfg
+
+
+def synthetic_table(level: float, seed: int = 15) -> np.ndarray:
+    """The float32 (15,)*6 stand-in value table of the tests and benchmarks (the real blobs are missing from the reference
+    checkout): 50/50 blend of seeded white noise and the FasTrack target sum_{i != 2} x_i^2 (Fastrack.py:296-306).
+    Same numbers as the product's hj_tables.synthetic_table (tests/test_abi_cpu.py checks it)."""
+    li = int(round(float(level) * 10.0))
+    rng = np.random.default_rng(seed * 1000 + li)
+    noise = rng.standard_normal((15,) * 6, dtype=np.float32)
+    g = grid_points()
+    target = np.zeros((15,) * 6, dtype=np.float64)
+    for dim in (0, 1, 3, 4, 5):
+        shape = [1] * 6
+        shape[dim] = 15
+        target = target + (g[dim] ** 2).reshape(shape)
+    return (0.5 * noise + 0.5 * target.astype(np.float32)).astype(np.float32)
 
 
 def grid_points() -> np.ndarray:
@@ -121,7 +179,7 @@ class OracleEnvs:
 
     def __init__(self, cfg: CfConfig, n: int, seed: int = 0, gid_base: int = 0):
         self.L = lib()
-        self.cfg = cfg.copy()
+        self.cfg = _cfg_copy(cfg)
         self.n = n
         self._buf = np.zeros(n * self.L.cfo_sizeof_env(), np.uint8)
         self.L.cfo_init_batch(_p(self._buf), n, C.byref(self.cfg), seed & (2 ** 64 - 1), gid_base)
