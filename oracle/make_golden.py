@@ -43,7 +43,17 @@ CASES = {
     'random_box_full': ('DroneHoverBulletEnvWithRandomAdversary-v0', {}, 200, 'hover', 5, None),
     'bullet_base_full': ('DroneHoverBulletEnv-v0', {}, 200, 'hover', 6, None),
     'target_randomhj_nodr': ('DroneHoverBulletEnvWithRandomHJAdversary-v0', dict(domain_randomization=-1), 200, 'mixed', 7, 15),
+    # BASELINE.json configs[3] with the ground-effect switch ON (physics.py:27-58, 118-120, 244-246; the reference never
+    # enables it): the reference object's own `physics.use_ground_effect` is set after construction; the 'descend'
+    # actions let the drone sink from ~1 m to the z < 0.2 m termination again and again, so the term grows from 4e-4 to
+    # 1e-2 of the thrust over the pre-states of the fixture
+    'initial_adv_ground': ('DroneHoverBulletEnvWithAdversaryInitial-v0', dict(use_ground_effect=1), 400, 'descend', 8, 15),
+    # non-default agent kwargs of DroneBaseEnv.__init__ (envs/base.py:26-47): latency, motor time constant, thrust noise
+    'free_adv15_agentkw': ('DroneHoverBulletFreeEnvWithAdversary-v0',
+                           dict(latency=0.012, motor_time_constant=0.12, motor_thrust_noise=0.10), 200, 'hover', 9, 15),
 }
+# kwargs of ours that the reference constructor does not take: applied to the reference object after construction
+POST_KWARGS = {'use_ground_effect': lambda env, v: setattr(env.unwrapped.physics, 'use_ground_effect', bool(v))}
 
 
 def actions_for(kind: str, steps: int, seed: int) -> np.ndarray:
@@ -52,6 +62,8 @@ def actions_for(kind: str, steps: int, seed: int) -> np.ndarray:
         return rng.uniform(-1, 1, (steps, 4)).astype(np.float32)
     hover = 2.0 / 1.8 - 1.0
     a = (hover + 0.05 * rng.standard_normal((steps, 4))).astype(np.float32)
+    if kind == 'descend':          # below hover thrust: sink to the ground-proximity termination, with a little attitude excitation
+        a = (hover - 0.12 + 0.05 * rng.standard_normal((steps, 4))).astype(np.float32)
     if kind == 'mixed':            # some out-of-range and wild actions to hit the clip / done paths
         wild = rng.uniform(-1.5, 1.5, (steps, 4)).astype(np.float32)
         pick = rng.uniform(size=steps) < 0.15
@@ -172,7 +184,10 @@ def run_case(name):
 
     np.random.seed(seed)
     with rh.table_dir(tables), rh.StdDrawRecorder() as rec:
-        env = rh.make_ref_env(env_id, **kwargs)
+        env = rh.make_ref_env(env_id, **{k: v for k, v in kwargs.items() if k not in POST_KWARGS})
+        for k, v in kwargs.items():
+            if k in POST_KWARGS:
+                POST_KWARGS[k](env, v)
         rec.take()
         state0 = record_of(env, 0.0)
         ep_ret = 0.0

@@ -86,7 +86,8 @@ def test_reset_parity_golden(name):
 DRIFT_BOUND_200 = 5e-3
 
 
-@pytest.mark.parametrize('name', ['free_without_clean', 'free_adv15_full', 'free_randomhj_full', 'initial_adv_full'])
+@pytest.mark.parametrize('name', ['free_without_clean', 'free_adv15_full', 'free_randomhj_full', 'initial_adv_full', 'initial_adv_ground',
+                                  'free_adv15_agentkw'])
 def test_rollout_drift_200_steps(name):
     """Free-running rollout (state carried on the GPU) over the first 200 events, same actions and draws."""
     import torch
