@@ -246,7 +246,7 @@ def main_ours(args):
         # global env ids: rank-major, then shard, so results do not depend on the number of GPUs;
         # one HJ table set per GPU, shared by its shards
         env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=(rank * S + s) * n,
-                   share_tables_with=shards[0] if shards else None, **env_kw)
+                   share_tables_with=shards[0] if shards else None, hj_tables='synthetic', **env_kw)
         shards.append(env)
     od = shards[0].obs_dim
     g = torch.Generator(device=dev).manual_seed(1 + rank)
@@ -569,7 +569,7 @@ def main_ppo(args):
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
     n, T = args.envs, 32
-    env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=rank * n, return_terminal_obs=True)
+    env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=rank * n, return_terminal_obs=True, hj_tables='synthetic')
     tr = PPOTrainer(env, rollout_len=T, epochs=300, seed=1)
     K, W = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
     for _ in range(W):

@@ -106,6 +106,8 @@ _SIGS = {
     'cf_raster_render_dev': (C.c_int, [_P, _P, _P, C.c_int32, _P, _P]),
     'cf_raster_render_host': (C.c_int, [_P, _P, _P, C.c_int32, _P]),
     'cf_get_poses_dev': (C.c_int, [_P, _P, C.c_int32, _P, _P]),
+    'cf_debug_draws': (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_int32, C.c_int32, _P, _P]),
+    'cf_debug_box_muller': (C.c_int, [C.c_int32, _P, C.c_int64, _P, _P]),
     'cf_launch_count': (C.c_int64, [_P]),
     'cf_kernel_timing': (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'cf_host_alloc': (_P, [C.c_uint64]),

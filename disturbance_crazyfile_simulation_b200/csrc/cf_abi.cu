@@ -63,6 +63,11 @@ struct cf_env {
     float* rec_dev = nullptr;        // scratch for get/set_state
     // host-pointer API: private stream + device mirrors of the caller's host buffers
     cudaStream_t hstream = nullptr;
+    // ordering between the two call families on one handle (both touch S): 1 = device-pointer API on the caller's stream,
+    // 2 = host-pointer API on hstream; on a switch the new stream waits for an event recorded on the previous one
+    cudaEvent_t order_ev = nullptr;
+    int last_family = 0;
+    cudaStream_t last_dev_stream = nullptr;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_cost = nullptr, *d_term = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
     bool tables_borrowed = false;    // tables belong to another handle (cf_share_hj_tables)
@@ -266,6 +271,17 @@ int check_tables(cf_env* e) {
     return CF_OK;
 }
 
+void order_families(cf_env* e, cudaStream_t st) {
+    const int family = st == e->hstream ? 2 : 1;
+    if (e->last_family && e->last_family != family && e->order_ev) {
+        cudaStream_t prev = e->last_family == 2 ? e->hstream : e->last_dev_stream;
+        if (cudaEventRecord(e->order_ev, prev) == cudaSuccess) cudaStreamWaitEvent(st, e->order_ev, 0);
+        else cudaGetLastError();                            // the caller's previous stream is gone: nothing left to order against
+    }
+    e->last_family = family;
+    if (family == 1) e->last_dev_stream = st;
+}
+
 int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint8_t* done, float* cost,
                 float* term_obs, uint8_t* truncated, cudaStream_t st) {
     if (!e || !act || !obs || !rew || !done || k < 1) return fail(CF_ERR_INVALID, "cf_step: null argument%s", "");
@@ -287,6 +303,7 @@ int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint
     if ((uintptr_t)act % 16 != 0) return fail(CF_ERR_INVALID, "cf_step: act must be 16-byte aligned%s", "");
     if ((uintptr_t)obs % 8 != 0 || (term_obs && (uintptr_t)term_obs % 8 != 0))
         return fail(CF_ERR_INVALID, "cf_step: obs rows must be 8-byte aligned%s", "");
+    order_families(e, st);
     EventPair* ep;
     begin_timing(e, st, &ep);
     cudaError_t lerr = launch_step(e->S, e->n, k, e->dev, e->tab, io, st);
@@ -377,6 +394,7 @@ int cf_create(const cf_config* cfg, int32_t n_envs, int32_t device, uint64_t see
     if (err == cudaSuccess) err = cudaMemset(e->value_ptrs_dev, 0, sizeof(float*) * CF_MAX_LEVELS);
     if (err == cudaSuccess) err = cudaMemcpy(e->thr_dev, thr, sizeof(thr), cudaMemcpyHostToDevice);
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->hstream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&e->order_ev, cudaEventDisableTiming);
     if (err == cudaSuccess) { launch_init(e->S, e->n_pad, e->dev, 0); e->launches += 1; err = cudaDeviceSynchronize(); }
     if (err != cudaSuccess) { cuda_fail(err, "cf_create"); cf_destroy(e); return err == cudaErrorMemoryAllocation ? CF_ERR_ALLOC : CF_ERR_CUDA; }
     e->tab.value = e->value_ptrs_dev; e->tab.signs = e->signs_slab; e->tab.thr = e->thr_dev;
@@ -395,6 +413,7 @@ int cf_destroy(cf_env* e) {
     cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
     cudaFree(e->d_done); cudaFree(e->d_trunc); cudaFree(e->d_mask);
     for (EventPair& p : e->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    if (e->order_ev) cudaEventDestroy(e->order_ev);
     if (e->hstream) cudaStreamDestroy(e->hstream);
     delete e;
     return CF_OK;
@@ -453,6 +472,7 @@ int cf_reset_dev(cf_env* e, const uint8_t* mask, float* obs, void* stream) {
     if (!e || !obs) return fail(CF_ERR_INVALID, "cf_reset: null argument%s", "");
     if (e->dev.injected && (!e->inj[2] || !e->inj[3])) return fail(CF_ERR_INVALID, "rng_mode INJECTED: call cf_set_noise_override first%s", "");
     CU(cudaSetDevice(e->device));
+    order_families(e, (cudaStream_t)stream);
     launch_reset(e->S, e->n, e->dev, mask, obs, e->inj[2], e->inj[3], (cudaStream_t)stream);
     e->launches += 1;
     CU(cudaGetLastError());
@@ -555,6 +575,45 @@ int cf_set_state(cf_env* e, const float* state_host) {
     launch_pack_state(e->S, e->n, e->rec_dev, 0);
     e->launches += 1;
     CU(cudaDeviceSynchronize());
+    return CF_OK;
+}
+
+int cf_debug_draws(cf_env* e, int32_t first_env, int32_t count, uint32_t ctr, uint32_t tag, int32_t nzb, int32_t nub,
+                   uint32_t* words_host, float* draws_host) {
+    if (!e || !words_host || !draws_host || count < 1 || first_env < 0 || nzb < 0 || nub < 0 || nzb + nub < 1 || nzb > 16)
+        return fail(CF_ERR_INVALID, "cf_debug_draws: bad argument%s", "");
+    CU(cudaSetDevice(e->device));
+    const size_t words = (size_t)count * (nzb + nub) * 4;
+    uint32_t* dw = nullptr; float* dd = nullptr;
+    cudaError_t err = cudaMalloc((void**)&dw, words * 4);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&dd, words * 4);
+    if (err == cudaSuccess) {
+        launch_debug_draws(e->dev, first_env, count, ctr, tag, nzb, nub, dw, dd, 0);
+        e->launches += 1;
+        err = cudaMemcpy(words_host, dw, words * 4, cudaMemcpyDeviceToHost);
+    }
+    if (err == cudaSuccess) err = cudaMemcpy(draws_host, dd, words * 4, cudaMemcpyDeviceToHost);
+    cudaFree(dw); cudaFree(dd);
+    if (err != cudaSuccess) return cuda_fail(err, "cf_debug_draws");
+    return CF_OK;
+}
+
+int cf_debug_box_muller(int32_t device, const uint32_t* words_host, int64_t n, float* normals_host, float* u01_host) {
+    if (!words_host || !normals_host || !u01_host || n < 1) return fail(CF_ERR_INVALID, "cf_debug_box_muller: bad argument%s", "");
+    CU(cudaSetDevice(device));
+    const size_t bytes = (size_t)n * 16;
+    uint32_t* dw = nullptr; float *dz = nullptr, *du = nullptr;
+    cudaError_t err = cudaMalloc((void**)&dw, bytes);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&dz, bytes);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&du, bytes);
+    if (err == cudaSuccess) err = cudaMemcpy(dw, words_host, bytes, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) {
+        launch_debug_box_muller(dw, n, dz, du, 0);
+        err = cudaMemcpy(normals_host, dz, bytes, cudaMemcpyDeviceToHost);
+    }
+    if (err == cudaSuccess) err = cudaMemcpy(u01_host, du, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(dw); cudaFree(dz); cudaFree(du);
+    if (err != cudaSuccess) return cuda_fail(err, "cf_debug_box_muller");
     return CF_OK;
 }
 

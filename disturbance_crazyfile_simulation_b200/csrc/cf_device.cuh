@@ -55,20 +55,23 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, const DevCfg& cfg) {
 __device__ __forceinline__ float u01(uint32_t w) {
     return __uint_as_float(0x3f800000u | (w >> 9)) - 0.99999994f;   // 1 - 2^-24, exact
 }
+// Box-Muller on the two word pairs of a Philox block: (r cos, r sin) with r = sqrt(-2 ln u0), angle pi (2 u1 - 1);
+// MUFU lg2 / sqrt / sin / cos.  tests/test_rng_bits.py sweeps every one of the 2^23 u01 values through this function
+// (cf_debug_box_muller) and states the error bound of the normals against float64.
+__device__ __forceinline__ float4 box_muller(uint4 w) {
+    float r0 = fsqrt(-1.3862943611f * __log2f(u01(w.x))), r1 = fsqrt(-1.3862943611f * __log2f(u01(w.z)));   // sqrt(-2 ln u)
+    float s0, c0_, s1, c1_;
+    __sincosf(kPi * (2.0f * u01(w.y) - 1.0f), &s0, &c0_);
+    __sincosf(kPi * (2.0f * u01(w.w) - 1.0f), &s1, &c1_);
+    return make_float4(r0 * c0_, r0 * s0, r1 * c1_, r1 * s1);
+}
 struct Rng {
     uint32_t c0, c1, c3;
     __device__ __forceinline__ uint4 raw(const DevCfg& cfg, uint32_t block) const {
         return philox4x32_10(make_uint4(c0, c1, block, c3), cfg);
     }
     // four standard normals of block b (Box-Muller on two pairs, same pairing as the oracle)
-    __device__ __forceinline__ float4 normals(const DevCfg& cfg, uint32_t b) const {
-        uint4 w = raw(cfg, b);
-        float r0 = fsqrt(-1.3862943611f * __log2f(u01(w.x))), r1 = fsqrt(-1.3862943611f * __log2f(u01(w.z)));   // sqrt(-2 ln u)
-        float s0, c0_, s1, c1_;
-        __sincosf(kPi * (2.0f * u01(w.y) - 1.0f), &s0, &c0_);
-        __sincosf(kPi * (2.0f * u01(w.w) - 1.0f), &s1, &c1_);
-        return make_float4(r0 * c0_, r0 * s0, r1 * c1_, r1 * s1);
-    }
+    __device__ __forceinline__ float4 normals(const DevCfg& cfg, uint32_t b) const { return box_muller(raw(cfg, b)); }
     __device__ __forceinline__ float4 uniforms(const DevCfg& cfg, uint32_t b) const {
         uint4 w = raw(cfg, 16u + b);
         return make_float4(u01(w.x), u01(w.y), u01(w.z), u01(w.w));

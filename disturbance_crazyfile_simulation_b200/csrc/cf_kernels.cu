@@ -465,6 +465,29 @@ __global__ void k_pd_actions(const float* __restrict__ obs, int obs_dim, int off
     reinterpret_cast<float4*>(act)[i] = a;
 }
 
+// Parity hooks for the production RNG path (tests/test_rng_bits.py): the raw Philox words and the standard draws of one
+// event, produced by the very device functions the step / reset kernels call (Rng::raw, u01, box_muller).
+// One thread per (env, block): blocks 0..nzb-1 are normal blocks, nzb..nzb+nub-1 the uniform blocks (counter 16 + b).
+__global__ void k_debug_draws(const __grid_constant__ DevCfg cfg, int first_env, int count, uint32_t ctr, uint32_t tag, int nzb,
+                              int nub, uint32_t* __restrict__ words, float* __restrict__ draws) {
+    const int nb = nzb + nub, t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count * nb) return;
+    const int j = t / nb, b = t - j * nb;
+    const Rng rng = make_rng(cfg.gid_base + first_env + j, ctr, tag);
+    const bool normal = b < nzb;
+    const uint4 w = rng.raw(cfg, normal ? (uint32_t)b : 16u + (uint32_t)(b - nzb));
+    const float4 v = normal ? rng.normals(cfg, (uint32_t)b) : rng.uniforms(cfg, (uint32_t)(b - nzb));
+    reinterpret_cast<uint4*>(words)[t] = w;
+    reinterpret_cast<float4*>(draws)[t] = v;
+}
+__global__ void k_debug_box_muller(const uint4* __restrict__ words, long long n, float4* __restrict__ z, float4* __restrict__ u) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const uint4 w = words[t];
+    z[t] = box_muller(w);
+    u[t] = make_float4(u01(w.x), u01(w.y), u01(w.z), u01(w.w));
+}
+
 // ---------------------------------------------------------------------------------- launchers
 static inline int blocks_for(int n, int threads) { return (n + threads - 1) / threads; }
 
@@ -556,6 +579,14 @@ void launch_gae(const float* rew, const float* val, const uint8_t* done, const f
                 cudaStream_t st) {
     k_gae<<<blocks_for(N, 128), 128, 0, st>>>(rew, val, done, end_val, last_val, gamma, lam, rew_scale, T, N, adv, tgt,
                                               disc_ret);
+}
+void launch_debug_draws(const DevCfg& cfg, int first_env, int count, uint32_t ctr, uint32_t tag, int nzb, int nub, uint32_t* words,
+                        float* draws, cudaStream_t st) {
+    k_debug_draws<<<blocks_for(count * (nzb + nub), 128), 128, 0, st>>>(cfg, first_env, count, ctr, tag, nzb, nub, words, draws);
+}
+void launch_debug_box_muller(const uint32_t* words, long long n, float* z, float* u, cudaStream_t st) {
+    k_debug_box_muller<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const uint4*>(words), n,
+                                                                   reinterpret_cast<float4*>(z), reinterpret_cast<float4*>(u));
 }
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st) {
     k_pd_actions<<<blocks_for(n, 128), 128, 0, st>>>(obs, obs_dim, off, n, act, g);

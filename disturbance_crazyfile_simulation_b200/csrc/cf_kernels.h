@@ -22,6 +22,9 @@ void launch_gather_poses(const float* S, int n, const int* idx, int count, float
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int T, int N, float* adv, float* tgt, float* disc_ret,
                 cudaStream_t st);
+void launch_debug_draws(const DevCfg& cfg, int first_env, int count, uint32_t ctr, uint32_t tag, int nzb, int nub, uint32_t* words,
+                        float* draws, cudaStream_t st);
+void launch_debug_box_muller(const uint32_t* words, long long n, float* z, float* u, cudaStream_t st);
 void set_error(const char* where, const char* what);     // cf_abi.cu: text behind cf_last_error()
 struct PdGains { float hover, kz, kvz, katt, krate, kyaw; };
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st);

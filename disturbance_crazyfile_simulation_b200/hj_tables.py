@@ -74,13 +74,52 @@ def tie_table(seed: int = 3) -> np.ndarray:
     return rng.integers(-1, 2, size=(GRID_PTS,) * 6).astype(np.float32)
 
 
-def load_table(level: float, table_dir: str | None = None, seed: int = 15) -> np.ndarray:
-    """Real table from ``table_dir`` when present (reference naming), else synthetic."""
+def _read_table(path: str) -> np.ndarray:
+    V = np.load(path)
+    if V.shape != (GRID_PTS,) * 6:
+        raise ValueError(f'{path}: expected shape {(GRID_PTS,) * 6}, got {V.shape}')
+    return np.ascontiguousarray(V, dtype=np.float32)
+
+
+def default_cache_dir() -> str:
+    return os.environ.get('CF_HJ_TABLE_CACHE') or os.path.join(os.path.expanduser('~'), '.cache',
+                                                               'disturbance_crazyfile_simulation_b200', 'hj_tables')
+
+
+def load_table(level: float, table_dir: str | None = None, seed: int | None = None, source: str | None = None,
+               device: int = 0) -> np.ndarray:
+    """The float32 ``(15,)*6`` value table of one disturbance level.
+
+    ``table_dir`` given: ``fastrack_{level}_15x15.npy`` from there, FileNotFoundError when absent - what ``np.load`` at
+    distur_gener.py:155 does.  Otherwise ``source`` (default: ``$CF_HJ_TABLES``, else ``'solve'``):
+      'solve'      the real table, generated once with the GPU solver (``hj_solver.solve_fastrack``, the reference's
+                   Fastrack.py problem) and cached under ``default_cache_dir()`` in the reference's file naming;
+      'synthetic'  the seeded stand-in of ``synthetic_table`` - an explicit opt-in for tests and benchmarks, never a
+                   silent fallback (a policy trained against it sees a random-sign torque, not the HJ-optimal one).
+    A ``seed`` without a ``source`` selects 'synthetic' (the fixtures name their table by seed)."""
     if table_dir is not None:
         path = os.path.join(table_dir, table_filename(level))
-        if os.path.exists(path):
-            V = np.load(path)
-            if V.shape != (GRID_PTS,) * 6:
-                raise ValueError(f'{path}: expected shape {(GRID_PTS,) * 6}, got {V.shape}')
-            return np.ascontiguousarray(V, dtype=np.float32)
-    return synthetic_table(level, seed)
+        if not os.path.exists(path):
+            raise FileNotFoundError(f'{path}: no HJ value table for disturbance level {level} (distur_gener.py:155); generate '
+                                    f'the tables with tools/make_hj_tables.py or pass hj_tables="solve" / "synthetic"')
+        return _read_table(path)
+    if source is None:
+        source = 'synthetic' if seed is not None else (os.environ.get('CF_HJ_TABLES') or 'solve')
+    if source == 'synthetic':
+        return synthetic_table(level, 15 if seed is None else seed)
+    if source != 'solve':
+        raise ValueError(f'hj_tables must be "solve", "synthetic" or a directory via hj_table_dir, got {source!r}')
+    cache = default_cache_dir()
+    path = os.path.join(cache, table_filename(level))
+    if os.path.exists(path):
+        return _read_table(path)
+    import sys
+    from . import hj_solver
+    print(f'[cf_b200] generating the HJ value table of disturbance level {level} on GPU {device} (a few seconds, cached in '
+          f'{cache})', file=sys.stderr)
+    V = hj_solver.solve_fastrack(level, device=device)
+    os.makedirs(cache, exist_ok=True)
+    tmp = f'{path}.{os.getpid()}.tmp.npy'
+    np.save(tmp, V)
+    os.replace(tmp, path)
+    return V

@@ -78,8 +78,8 @@ class CrazyFlieVecEnv:
     """
 
     def __init__(self, env_id: str, num_envs: int = 1, device: Optional[int] = None, seed: int = 0,
-                 env_id_base: int = 0, hj_table_dir: Optional[str] = None, hj_table_seed: int = 15,
-                 return_terminal_obs: bool = False, share_tables_with: Optional['CrazyFlieVecEnv'] = None, **kwargs):
+                 env_id_base: int = 0, hj_table_dir: Optional[str] = None, hj_table_seed: Optional[int] = None,
+                 hj_tables: Optional[str] = None, return_terminal_obs: bool = False, share_tables_with: Optional['CrazyFlieVecEnv'] = None, **kwargs):
         L = abi.lib()
         if not torch.cuda.is_available():
             raise RuntimeError('CrazyFlieVecEnv needs a CUDA device (no CPU fallback)')
@@ -119,7 +119,7 @@ class CrazyFlieVecEnv:
         if share_tables_with is not None:
             abi.check(L.cf_share_hj_tables(self._h, share_tables_with._h))
         else:
-            self._load_tables(hj_table_dir, hj_table_seed)
+            self._load_tables(hj_table_dir, hj_table_seed, hj_tables)
 
     # ------------------------------------------------------------------ tables
     def _needed_levels(self):
@@ -131,9 +131,12 @@ class CrazyFlieVecEnv:
             return [level_index(l) for l in LEVELS if l > 0]
         return []
 
-    def _load_tables(self, table_dir, seed):
+    def _load_tables(self, table_dir, seed, source):
+        """Value tables of the levels this env can draw (hj_tables.load_table): files from ``hj_table_dir`` (missing file
+        = FileNotFoundError, as np.load at distur_gener.py:155), else ``hj_tables='solve'`` (default: real tables from the
+        GPU solver, cached) or the explicit opt-in ``hj_tables='synthetic'`` / ``hj_table_seed=...`` of tests and benchmarks."""
         for li in self._needed_levels():
-            self.load_hj_table(li / 10.0, load_table(li / 10.0, table_dir, seed))
+            self.load_hj_table(li / 10.0, load_table(li / 10.0, table_dir, seed, source, self.device_index))
 
     def load_hj_table(self, level: float, V: np.ndarray) -> None:
         """np.load(fastrack_{level}_15x15.npy) of distur_gener.py:155, hoisted out of the step."""

@@ -316,6 +316,19 @@ int64_t cf_launch_count(const cf_env* env);
  * measured with CUDA events on the launching stream when profiling was enabled */
 int cf_kernel_timing(cf_env* env, int32_t enable, int32_t reset, double* avg_ms, int64_t* launches);
 
+/* Parity hooks for the production RNG path (rng_mode = CF_RNG_PHILOX), host pointers, synchronous.
+ * cf_debug_draws: the raw Philox4x32-10 words and the standard draws of ONE event of envs first_env .. first_env+count-1,
+ * produced by the device functions the step / reset kernels call.  An event is (global env id, event counter, tag):
+ * tag 0 = step, 1 = in-place reset inside a step launch, 2 = cf_reset_*, 3 = constructor-time gyro-bias draw; the
+ * counter is the env's CF_S_RNG_CTR word when the event runs.  Blocks 0..n_norm_blocks-1 are normal blocks (Philox
+ * counter word 2 = b; four normals each by Box-Muller), the following n_unif_blocks are uniform blocks (counter word 2 =
+ * 16 + b).  words_host [count][n_norm_blocks+n_unif_blocks][4] uint32, draws_host the same shape in float32.
+ * cf_debug_box_muller: the normals [n][4] and the u01 values [n][4] the kernels derive from given raw words [n][4]
+ * (no handle needed): lets a test sweep all 2^23 mantissa patterns. */
+int cf_debug_draws(cf_env* env, int32_t first_env, int32_t count, uint32_t event_ctr, uint32_t tag, int32_t n_norm_blocks,
+                   int32_t n_unif_blocks, uint32_t* words_host, float* draws_host);
+int cf_debug_box_muller(int32_t device, const uint32_t* words_host, int64_t n, float* normals_host, float* u01_host);
+
 /* Tracing hook: when `trace_dev` (DEVICE pointer, [cf_num_tiles][16] uint64, caller-owned, zeroed by the caller)
  * is set, every step launch records per tile (times in %globaltimer ns): [0] SM id, [1] CTA start, [2] state tile
  * landed in shared memory, [3..6] warp 0..3 finished the step phase, [7] tile barrier passed, [8] in-place resets

@@ -40,7 +40,7 @@ def main():
     n, S = a.envs, a.shards
     shards = []
     for s in range(S):
-        shards.append(make(a.env_id, num_envs=n, seed=2024, env_id_base=s * n,
+        shards.append(make(a.env_id, num_envs=n, seed=2024, env_id_base=s * n, hj_tables='synthetic',
                            share_tables_with=shards[0] if shards else None, **kw))
     od = shards[0].obs_dim
     g = torch.Generator(device=dev).manual_seed(1)

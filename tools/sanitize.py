@@ -16,7 +16,7 @@ from disturbance_crazyfile_simulation_b200 import make  # noqa: E402
 from disturbance_crazyfile_simulation_b200.gae import gae  # noqa: E402
 
 env_id, n = 'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0', 1000
-a = make(env_id, num_envs=n, seed=1, return_terminal_obs=True)
+a = make(env_id, num_envs=n, seed=1, return_terminal_obs=True, hj_tables='synthetic')
 b = make(env_id, num_envs=n, seed=1, env_id_base=n, share_tables_with=a)
 acts = [torch.rand((n, 4), device='cuda') * 2 - 1 for _ in range(2)]
 a.set_prefetch_next(b, acts[1]); b.set_prefetch_next(a, acts[0])
