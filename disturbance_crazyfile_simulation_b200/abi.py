@@ -63,6 +63,14 @@ class CfError(RuntimeError):
 
 
 _P = C.c_void_p
+
+
+class CfPolicyWeights(C.Structure):
+    """``cf_policy_weights`` of include/cf_abi.h (device pointers)."""
+    _fields_ = [('obs_mean', C.c_void_p), ('obs_std', C.c_void_p),
+                ('pi_w', C.c_void_p * 3), ('pi_b', C.c_void_p * 3), ('v_w', C.c_void_p * 3), ('v_b', C.c_void_p * 3),
+                ('log_std', C.c_void_p), ('pi_hidden', C.c_int32), ('v_hidden', C.c_int32), ('obs_eps', C.c_float),
+                ('reserved', C.c_int32)]
 _SIGS = {
     'cf_abi_version': (C.c_int, []),
     'cf_last_error': (C.c_char_p, []),
@@ -100,6 +108,7 @@ _SIGS = {
     'cf_hj_solver_update': (C.c_int, [_P, C.c_float, C.c_float, _P, _P]),
     'cf_hj_solver_run': (C.c_int, [_P, C.c_double, C.c_double, C.c_int64, _P, _P]),
     'cf_hj_solver_timing': (C.c_int, [_P, _P, _P]),
+    'cf_policy_step_dev': (C.c_int, [_P, _P, _P, C.c_int32, _P, _P, _P, _P]),
     'cf_pd_actions_dev': (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P]),
     'cf_raster_create': (C.c_int, [_P, C.c_int32, _P, _P, C.c_int32, C.c_float]),
     'cf_raster_destroy': (None, [_P]),
@@ -108,6 +117,7 @@ _SIGS = {
     'cf_get_poses_dev': (C.c_int, [_P, _P, C.c_int32, _P, _P]),
     'cf_debug_draws': (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_int32, C.c_int32, _P, _P]),
     'cf_debug_box_muller': (C.c_int, [C.c_int32, _P, C.c_int64, _P, _P]),
+    'cf_debug_euler': (C.c_int, [C.c_int32, _P, C.c_int64, _P, _P]),
     'cf_launch_count': (C.c_int64, [_P]),
     'cf_kernel_timing': (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'cf_host_alloc': (_P, [C.c_uint64]),

@@ -617,6 +617,24 @@ int cf_debug_box_muller(int32_t device, const uint32_t* words_host, int64_t n, f
     return CF_OK;
 }
 
+int cf_debug_euler(int32_t device, const float* quat_host, int64_t n, float* rpy_bullet_host, float* rpy_hj_host) {
+    if (!quat_host || !rpy_bullet_host || !rpy_hj_host || n < 1) return fail(CF_ERR_INVALID, "cf_debug_euler: bad argument%s", "");
+    CU(cudaSetDevice(device));
+    float *dq = nullptr, *da = nullptr, *db = nullptr;
+    cudaError_t err = cudaMalloc((void**)&dq, (size_t)n * 16);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&da, (size_t)n * 12);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&db, (size_t)n * 12);
+    if (err == cudaSuccess) err = cudaMemcpy(dq, quat_host, (size_t)n * 16, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) {
+        launch_debug_euler(dq, n, da, db, 0);
+        err = cudaMemcpy(rpy_bullet_host, da, (size_t)n * 12, cudaMemcpyDeviceToHost);
+    }
+    if (err == cudaSuccess) err = cudaMemcpy(rpy_hj_host, db, (size_t)n * 12, cudaMemcpyDeviceToHost);
+    cudaFree(dq); cudaFree(da); cudaFree(db);
+    if (err != cudaSuccess) return cuda_fail(err, "cf_debug_euler");
+    return CF_OK;
+}
+
 int cf_get_poses_dev(cf_env* e, const int32_t* env_idx_dev, int32_t count, float* poses_dev, void* stream) {
     if (!e || !poses_dev || count < 0) return fail(CF_ERR_INVALID, "cf_get_poses_dev: bad argument%s", "");
     if (count == 0) return CF_OK;
@@ -708,6 +726,30 @@ int cf_gae_dev(const float* rew, const float* val, const uint8_t* done, const fl
     if (!rew || !val || !done || !last_val || !adv || !target_v || !disc_ret || T < 1 || N < 1)
         return fail(CF_ERR_INVALID, "cf_gae: bad argument%s", "");
     launch_gae(rew, val, done, end_val, last_val, gamma, lam, rew_scale, T, N, adv, target_v, disc_ret, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
+int cf_policy_step_dev(cf_env* e, const cf_policy_weights* w, const float* obs, int32_t deterministic, float* act, float* val,
+                       float* logp, void* stream) {
+    if (!e || !w || !obs || !act || !val || !logp) return fail(CF_ERR_INVALID, "cf_policy_step: null argument%s", "");
+    if (w->pi_hidden < 1 || w->pi_hidden > 64 || w->v_hidden < 1 || w->v_hidden > 64)
+        return fail(CF_ERR_INVALID, "cf_policy_step: hidden widths must be 1..64%s", "");
+    for (int l = 0; l < 3; ++l)
+        if (!w->pi_w[l] || !w->pi_b[l] || !w->v_w[l] || !w->v_b[l]) return fail(CF_ERR_INVALID, "cf_policy_step: null weight pointer%s", "");
+    if (!deterministic && !w->log_std) return fail(CF_ERR_INVALID, "cf_policy_step: log_std needed for sampling%s", "");
+    if (((uintptr_t)obs & 7) || ((uintptr_t)act & 15)) return fail(CF_ERR_INVALID, "cf_policy_step: obs must be 8-byte, act 16-byte aligned%s", "");
+    CU(cudaSetDevice(e->device));
+    order_families(e, (cudaStream_t)stream);                 // reads the event counters the step kernels write
+    PolicyHostArgs h;
+    h.obs = obs; h.obs_mean = w->obs_mean; h.obs_std = w->obs_std;
+    for (int l = 0; l < 3; ++l) { h.pi_w[l] = w->pi_w[l]; h.pi_b[l] = w->pi_b[l]; h.v_w[l] = w->v_w[l]; h.v_b[l] = w->v_b[l]; }
+    h.log_std = w->log_std; h.S = e->S; h.act = act; h.val = val; h.logp = logp;
+    h.n = e->n; h.obs_dim = e->obs_dim; h.pi_h = w->pi_hidden; h.v_h = w->v_hidden; h.deterministic = deterministic ? 1 : 0;
+    h.eps = w->obs_eps;
+    cudaError_t err = launch_policy(h, e->dev, (cudaStream_t)stream);
+    if (err != cudaSuccess) return cuda_fail(err, "launch_policy");
+    e->launches += 1;
     CU(cudaGetLastError());
     return CF_OK;
 }

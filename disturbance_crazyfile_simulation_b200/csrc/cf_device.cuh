@@ -122,23 +122,35 @@ __device__ __forceinline__ DrawSrc make_draws(const DevCfg& cfg, long long gid, 
 }
 
 // ---------------------------------------------------------------------------------- state access
-// Word w of this thread's env: p[w * CF_TILE].  p points into the shared-memory copy of the tile
-// (step kernel, words 0..CF_DYN_WORDS-1) or into the tile in HBM (all 76 words).
+// Word w (CF_S_* of cf_abi.h) of this thread's env.  `p` addresses the words the step kernel stages in shared memory
+// (device words 0..CF_BULK_WORDS-1) - or the whole tile in HBM for the reset / init kernels -, `h` the tile in HBM for the
+// history words (device words CF_BULK_WORDS..CF_DYN_WORDS-1), which never go through shared memory.  Both at stride CF_TILE.
+// w is a compile-time constant at every call site (after unrolling), so the choice of pointer and the word permutation fold.
 struct EnvRef {
     float* p;
-    __device__ __forceinline__ float f(int w) const { return p[w * CF_TILE]; }
-    __device__ __forceinline__ void f(int w, float v) const { p[w * CF_TILE] = v; }
-    __device__ __forceinline__ uint32_t u(int w) const { return __float_as_uint(p[w * CF_TILE]); }
-    __device__ __forceinline__ void u(int w, uint32_t v) const { p[w * CF_TILE] = __uint_as_float(v); }
+    float* h;
+    __device__ __forceinline__ float* at(int w) const {
+        const int d = cf_dev_word(w);
+        return ((d >= CF_BULK_WORDS && d < CF_DYN_WORDS) ? h : p) + d * CF_TILE;
+    }
+    __device__ __forceinline__ float f(int w) const { return *at(w); }
+    __device__ __forceinline__ void f(int w, float v) const { *at(w) = v; }
+    __device__ __forceinline__ uint32_t u(int w) const { return __float_as_uint(*at(w)); }
+    __device__ __forceinline__ void u(int w, uint32_t v) const { *at(w) = __uint_as_float(v); }
     __device__ __forceinline__ void get3(int w, float v[3]) const { v[0] = f(w); v[1] = f(w + 1); v[2] = f(w + 2); }
     __device__ __forceinline__ void get4(int w, float v[4]) const { v[0] = f(w); v[1] = f(w + 1); v[2] = f(w + 2); v[3] = f(w + 3); }
     __device__ __forceinline__ void set3(int w, const float v[3]) const { f(w, v[0]); f(w + 1, v[1]); f(w + 2, v[2]); }
     __device__ __forceinline__ void set4(int w, const float v[4]) const { f(w, v[0]); f(w + 1, v[1]); f(w + 2, v[2]); f(w + 3, v[3]); }
+    // four consecutive words below CF_S_ACT_PREV1 at a RUN-TIME word index (device order == record order there)
+    __device__ __forceinline__ void get4_low(int w, float v[4]) const {
+        v[0] = p[w * CF_TILE]; v[1] = p[(w + 1) * CF_TILE]; v[2] = p[(w + 2) * CF_TILE]; v[3] = p[(w + 3) * CF_TILE];
+    }
 };
 // global-memory address of env i's word 0 in the tiled state array
 __device__ __forceinline__ float* env_global(float* S, int i) {
     return S + (size_t)(i / CF_TILE) * (CF_STATE_WORDS * CF_TILE) + (i % CF_TILE);
 }
+__device__ __forceinline__ EnvRef env_ref_global(float* S, int i) { float* g = env_global(S, i); return EnvRef{g, g}; }
 
 // domain-randomised parameters (words CF_S_DT..): read-only in the step, rewritten by reset
 struct DrParams {
@@ -191,18 +203,40 @@ __device__ __forceinline__ void matTvec(const float R[9], const float v[3], floa
     o[1] = R[1] * v[0] + R[4] * v[1] + R[7] * v[2];
     o[2] = R[2] * v[0] + R[5] * v[1] + R[8] * v[2];
 }
+// atan2 / asin without libdevice's IEEE division and special-case paths (the two Euler conversions of a step were 306
+// warp-instructions of atan2f / asinf).  atan(a) / a on a in [0, 1] as a degree-8 polynomial in a^2 (weighted minimax fit,
+// coefficients from a Lawson iteration in float64): max |error| of the assembled atan2 over the circle 1.6e-7 rad = at most
+// 2 ulp of the result for |angle| >= pi/8, absolute 1.6e-7 below (tests/test_gpu_parity.py::test_fast_atan2_asin).
+// atan2(0, 0) = 0 like libm; NaN in, NaN out.
+__device__ __forceinline__ float atan2_fast(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(fmaxf(ax, ay), 1e-30f), mn = fminf(ax, ay);
+    const float a = mn * frcp(mx), t = a * a;
+    float q = 2.479950796e-03f;
+    q = fmaf(q, t, -1.449995057e-02f); q = fmaf(q, t, 3.995352576e-02f); q = fmaf(q, t, -7.250832014e-02f);
+    q = fmaf(q, t, 1.050737913e-01f); q = fmaf(q, t, -1.416375388e-01f); q = fmaf(q, t, 1.998630745e-01f);
+    q = fmaf(q, t, -3.333262557e-01f); q = fmaf(q, t, 9.999998923e-01f);
+    float r = a * q;
+    r = ay > ax ? 0.5f * kPi - r : r;
+    r = x < 0.0f ? kPi - r : r;
+    return copysignf(r, y);
+}
+// asin(x) = atan2(x, sqrt((1 - x)(1 + x))) for |x| <= 1 (1 - x is exact for x >= 0.5: no cancellation near the ends)
+__device__ __forceinline__ float asin_fast(float x) { return atan2_fast(x, fsqrt((1.0f - x) * (1.0f + x))); }
+
 // pybullet.getEulerFromQuaternion (agents.py:446) incl. the gimbal branch at |sin pitch| >= 0.99999
 __device__ __forceinline__ void quat_to_rpy_bullet(const float q[4], float rpy[3]) {
     float x = q[0], y = q[1], z = q[2], w = q[3];
     float sqx = x * x, sqy = y * y, sqz = z * z, squ = w * w;
     float sarg = -2.0f * (x * z - w * y);
-    if (sarg <= -0.99999f) { rpy[0] = 0.f; rpy[1] = -0.5f * kPi; rpy[2] = 2.f * atan2f(x, -y); }
-    else if (sarg >= 0.99999f) { rpy[0] = 0.f; rpy[1] = 0.5f * kPi; rpy[2] = 2.f * atan2f(-x, y); }
-    else {
-        rpy[0] = atan2f(2.f * (y * z + w * x), squ - sqx - sqy + sqz);
-        rpy[1] = asinf(sarg);
-        rpy[2] = atan2f(2.f * (x * y + w * z), squ + sqx - sqy - sqz);
-    }
+    // one atan2 body for both cases: in the gimbal branches roll = 0 and yaw = 2 atan2(+-x, -+y)
+    const bool lo = sarg <= -0.99999f, hi = sarg >= 0.99999f, gimbal = lo || hi;
+    const float ry = gimbal ? (lo ? x : -x) : 2.f * (x * y + w * z);
+    const float rx = gimbal ? (lo ? -y : y) : squ + sqx - sqy - sqz;
+    const float yaw = atan2_fast(ry, rx);
+    rpy[2] = gimbal ? 2.f * yaw : yaw;
+    rpy[1] = gimbal ? (lo ? -0.5f * kPi : 0.5f * kPi) : asin_fast(fminf(1.0f, fmaxf(-1.0f, sarg)));
+    rpy[0] = gimbal ? 0.f : atan2_fast(2.f * (y * z + w * x), squ - sqx - sqy + sqz);
 }
 // sin and cos for |x| <= pi/2 (half angles of clipped Euler angles): Taylor polynomials to x^11 / x^12,
 // truncation < 6e-8 relative at the interval end; no range reduction, no slow path.
@@ -239,11 +273,11 @@ __device__ __forceinline__ void rpy_to_quat(const float rpy[3], float q[4]) {
 // quat2euler of distur_gener.py:186-207
 __device__ __forceinline__ void quat2euler_hj(const float q[4], float out[3]) {
     float x = q[0], y = q[1], z = q[2], w = q[3];
-    out[0] = atan2f(2.0f * (w * x + y * z), 1.0f - 2.0f * (x * x + y * y));
+    out[0] = atan2_fast(2.0f * (w * x + y * z), 1.0f - 2.0f * (x * x + y * y));
     float t2 = 2.0f * (w * y - z * x);
     t2 = fminf(1.0f, fmaxf(-1.0f, t2));
-    out[1] = asinf(t2);
-    out[2] = atan2f(2.0f * (w * z + x * y), 1.0f - 2.0f * (y * y + z * z));
+    out[1] = asin_fast(t2);
+    out[2] = atan2_fast(2.0f * (w * z + x * y), 1.0f - 2.0f * (y * y + z * z));
 }
 
 // ---------------------------------------------------------------------------------- HJ lookup
@@ -752,67 +786,42 @@ __device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const 
     }
 }
 
-// Standard draws of a step event, produced BEFORE the state tile has landed (they depend on the env id and
-// the event counter only): normal blocks 0..3 in registers, blocks 4..10 and the six observation uniforms in
-// `s` - 34 words of warp-local shared-memory scratch, word-major ([slot][lane], conflict-free), which is the
-// warp's own 32 observation rows: they are written only after the last draw has been read.
+// The 44 standard normals of a step event, generated ahead of their use into shared-memory scratch (they depend on the env
+// id and the event counter only): slot k of this lane = normal k.  Slots 0..31 live in the warp's own 32 observation rows,
+// word-major ([slot][lane], conflict-free, lane-private; the rows are written only after the last slot has been read), slots
+// 32..43 in the CTA's extra scratch ([slot][thread]).  Slots 0..20 are reused late in the step: once the physics and the gyro
+// samples have consumed z[0:26], the env's 21 history words are copied into them asynchronously from HBM (step_env).
+// The step's six live uniforms are generated where the observation is assembled; they never touch shared memory.
+#define CF_DRAW_BLOCKS (CF_STEP_NORMALS / 4)   /* 11 Philox blocks */
+#define CF_ROW_SLOTS 32
+#define CF_EXTRA_SLOTS (4 * CF_DRAW_BLOCKS - CF_ROW_SLOTS)
 struct StepDraws {
-    float4 r0, r1, r2, r3;
-    float ubox0, ubox1;
-    const float* s;
+    float* s;             // s[k * 32]: slot k < 32
+    float* x;             // x[(k - 32) * CF_TILE]: slot k >= 32
+    __device__ __forceinline__ float* slot(int k) const { return k < CF_ROW_SLOTS ? s + k * 32 : x + (k - CF_ROW_SLOTS) * CF_TILE; }
+    __device__ __forceinline__ void put(int b, float4 v) const {     // b: run-time block index
+        float* p = slot(4 * b);
+        const int st = 4 * b < CF_ROW_SLOTS ? 32 : CF_TILE;
+        p[0] = v.x; p[st] = v.y; p[2 * st] = v.z; p[3 * st] = v.w;
+    }
     template <int B>
     __device__ __forceinline__ float4 z() const {
-        if (B == 0) return r0;
-        if (B == 1) return r1;
-        if (B == 2) return r2;
-        if (B == 3) return r3;
-        const float* p = s + (4 * (B - 4)) * 32;
-        return make_float4(p[0], p[32], p[64], p[96]);
-    }
-    __device__ __forceinline__ void obs_uniforms(float u[6]) const {
-#pragma unroll
-        for (int i = 0; i < 6; ++i) u[i] = s[(28 + i) * 32];
+        const float* p = slot(4 * B);
+        constexpr int st = 4 * B < CF_ROW_SLOTS ? 32 : CF_TILE;
+        return make_float4(p[0], p[st], p[2 * st], p[3 * st]);
     }
 };
-// PART 0: blocks 0..5 (+ the random-box uniforms); PART 1: blocks 6..10 and the observation uniforms.  The step
-// kernel runs part 0 while the tile is in flight and part 1 behind the HJ table gather.
-#ifndef CF_RNG_UNROLL
-#define CF_RNG_UNROLL 1
-#endif
-template <bool NOISE, int PART>
-__device__ __forceinline__ void pregen_step_draws(const DrawSrc& dw, const DevCfg& cfg, float* scratch, StepDraws& sd) {
-    if (PART == 0) {
-        sd.s = scratch;
-        sd.ubox0 = sd.ubox1 = 0.0f;
-        sd.r0 = dw.z(cfg, 0);
-        sd.r3 = dw.z(cfg, 3);
-        if (NOISE) { sd.r1 = dw.z(cfg, 1); sd.r2 = dw.z(cfg, 2); }
-        else sd.r1 = sd.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    if (NOISE) {
-        // not unrolled: each Philox + Box-Muller body is ~2.2 KB of code and the step's executed path already overflows the
-        // 32 KB instruction cache (ncu: 39 % of the stall samples are no_instruction); one body for the seven blocks is
-        // 14 KB less code and measured +2 % (A/B on one box, -DCF_RNG_UNROLL=... rebuilds the unrolled form)
-        CF_UNROLL_N_(CF_RNG_UNROLL)
-        for (int b = (PART == 0 ? 4 : 6); b < (PART == 0 ? 6 : 11); ++b) {
-            float4 v = dw.z(cfg, b);
-            float* p = scratch + (4 * (b - 4)) * 32;
-            p[0] = v.x; p[32] = v.y; p[64] = v.z; p[96] = v.w;
-        }
-        if (PART == 1) {
-            float4 u0 = dw.u(cfg, 0), u1 = dw.u(cfg, 1);
-            scratch[28 * 32] = u0.x; scratch[29 * 32] = u0.y; scratch[30 * 32] = u0.z; scratch[31 * 32] = u0.w;
-            scratch[32 * 32] = u1.x; scratch[33 * 32] = u1.y;
-        } else if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {
-            float4 u1 = dw.u(cfg, 1);
-            sd.ubox0 = u1.z; sd.ubox1 = u1.w;
-        }
-    } else if (PART == 0) {
-        float4 v = dw.z(cfg, 4);                            // only z[16] (OU, substep 2) is live without sensor noise
-        scratch[0] = v.x; scratch[32] = v.y; scratch[64] = v.z; scratch[96] = v.w;
-        if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) { float4 u1 = dw.u(cfg, 1); sd.ubox0 = u1.z; sd.ubox1 = u1.w; }
-    }
+// which normal blocks of a step event are live: all 11 with sensor noise; without it the OU draws z[0:4] (block 0) and z[13:17]
+// (blocks 3, 4)
+template <bool NOISE>
+__device__ __forceinline__ bool step_block_live(int b) { return NOISE || b == 0 || b == 3 || b == 4; }
+
+// 4-byte asynchronous copy global -> shared without committing a group (LDGSTS); cp_async_commit closes the group
+__device__ __forceinline__ void cp_async_4_nocommit(float* dst_smem, const float* src_gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src_gmem) : "memory");
 }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // The HJ table fetch of a step, issued from the tile as soon as it has landed (step_env consumes it).
 template <int HJ_MODE>
@@ -843,7 +852,7 @@ struct StepOut {
 // e: dynamic words (shared memory in the step kernel); p: the env's domain-randomised parameters.
 template <bool NOISE, int HJ_MODE>
 __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, const DevCfg& cfg, const DevTables& tab,
-                                            const HjFetch& hjf, const float a[4], const StepDraws& dw, float* row,
+                                            const HjFetch& hjf, const float a[4], const StepDraws& dw, const DrawSrc& src, float* row,
                                             unsigned wmask) {
     constexpr int OD = NOISE ? 34 : 42;
     const uint32_t misc = e.u(CF_S_MISC);
@@ -857,15 +866,16 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame of the pre-step state: HJ lookup and substep 1
     float d0 = 0.0f, d1 = 0.0f;
     if (cfg.dstb_kind == CF_DSTB_RANDOM_BOX) {                // dstb_space.sample(), hover_free.py:868-878
-        d0 = unif(-1e-3f, 1e-3f, dw.ubox0);
-        d1 = unif(-1e-3f, 1e-3f, dw.ubox1);
+        const float4 ub = src.u(cfg, 1);                    // u[6], u[7] of the event
+        d0 = unif(-1e-3f, 1e-3f, ub.z);
+        d1 = unif(-1e-3f, 1e-3f, ub.w);
     }
     e.get3(CF_S_POS, b.pos); e.get3(CF_S_VEL, b.vel); e.get4(CF_S_MOTOR_X, b.x); e.get4(CF_S_OU, b.ou);
     // latency ring (agents.py:268-276): substep 1 reads slot ring_idx, substep 2 the other one; both
     // are overwritten with the new action and ring_idx returns to its value
     const int ridx = misc_ring(misc) & 1;
     float del1[4], del2[4];
-    e.get4(CF_S_RING + 4 * ridx, del1); e.get4(CF_S_RING + 4 * (ridx ^ 1), del2);
+    e.get4_low(CF_S_RING + 4 * ridx, del1); e.get4_low(CF_S_RING + 4 * (ridx ^ 1), del2);
     const float invJ[3] = {frcp(p.J[0]), frcp(p.J[1]), frcp(p.J[2])};
     const float invm = frcp(p.mass);
     float bias[3], lpf[3];
@@ -900,49 +910,72 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     float rpy[3];
     quat_to_rpy_bullet(b.quat, rpy);
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);
+    float4 z5, z6;
+    if (NOISE) {
+        z5 = dw.z<5>(); z6 = dw.z<6>();
+        const float zb[3] = {z4.y, z4.z, z4.w}, zr[3] = {z5.x, z5.y, z5.z}, zt[3] = {z5.w, z6.x, z6.y};
+        gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
+    }
+    // The 21 history words (u(k-1), u(k-2), last emitted obs13: device words 39..59 of the tile in HBM, L2-prefetched at CTA
+    // start) are only copied through into the row.  Draw slots 0..25 of this lane are dead by now (z[0:26] consumed): the words
+    // land there by asynchronous copy - no register is held and nothing waits while the observation below is computed.
+    float* const hs = dw.s;
+#ifndef CF_PROBE_NOHIST                                       /* tools/ only (wrong results): the step without its history loads */
+#pragma unroll
+    for (int k = 0; k < CF_HIST_WORDS; ++k) cp_async_4_nocommit(hs + k * 32, e.h + (CF_BULK_WORDS + k) * CF_TILE);
+    cp_async_commit();
+#endif
     // compute_history, base.py:305-321.  Action history with the reference's aliased view of
     // action_buffer[-1,:] in the first two steps of an episode (agents.py:386, base.py:459-460):
     // [a,a] then [a,u(k-1)] then normal
     const bool first = ep_len == 0, second = ep_len == 1;
+    float hist[OD], on[13];
+    if (NOISE) {
+        float4 z7 = dw.z<7>(), z8 = dw.z<8>(), z9 = dw.z<9>(), z10 = dw.z<10>();
+        const float z[18] = {z6.z, z6.w, z7.x, z7.y, z7.z, z7.w, z8.x, z8.y, z8.z, z8.w, z9.x, z9.y, z9.z, z9.w,
+                             z10.x, z10.y, z10.z, z10.w};
+        const float4 u0 = src.u(cfg, 0), u1 = src.u(cfg, 1);   // u[0:6]: position and attitude uniforms of the observation
+        const float u[6] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y};
+        observe_full(b.pos, b.vel, rpy, wb, bias, lpf, cfg, z, u, on);
+        e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { on[i] = b.pos[i]; on[7 + i] = b.vel[i]; on[10 + i] = wb[i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) on[3 + i] = b.quat[i];
+    }
+    cp_async_wait_all();
     float ap1[4], ap2[4], h0[4], h1[4];
-    e.get4(CF_S_ACT_PREV1, ap1); e.get4(CF_S_ACT_PREV2, ap2);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        ap1[i] = hs[(cf_dev_word(CF_S_ACT_PREV1) - CF_BULK_WORDS + i) * 32];
+        ap2[i] = hs[(cf_dev_word(CF_S_ACT_PREV2) - CF_BULK_WORDS + i) * 32];
+    }
+#pragma unroll
+    for (int i = 0; i < 13; ++i) hist[i] = hs[(cf_dev_word(CF_S_OBS_PREV) - CF_BULK_WORDS + i) * 32];
+#ifdef CF_PROBE_NOHIST
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { ap1[i] = a[i]; ap2[i] = a[i]; }
+#endif
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         h0[i] = (first || second) ? a[i] : ap2[i];
         h1[i] = first ? a[i] : ap1[i];
     }
     e.set4(CF_S_ACT_PREV2, ap1); e.set4(CF_S_ACT_PREV1, a);
-    float hist[OD];
 #pragma unroll
-    for (int i = 0; i < 13; ++i) hist[i] = e.f(CF_S_OBS_PREV + i);
+    for (int i = 0; i < 13; ++i) e.f(CF_S_OBS_PREV + i, on[i]);
     if (NOISE) {
-        float4 z5 = dw.z<5>(), z6 = dw.z<6>();
-        {
-            const float zb[3] = {z4.y, z4.z, z4.w}, zr[3] = {z5.x, z5.y, z5.z}, zt[3] = {z5.w, z6.x, z6.y};
-            gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
-        }
-        float4 z7 = dw.z<7>(), z8 = dw.z<8>(), z9 = dw.z<9>(), z10 = dw.z<10>();
-        const float z[18] = {z6.z, z6.w, z7.x, z7.y, z7.z, z7.w, z8.x, z8.y, z8.z, z8.w, z9.x, z9.y, z9.z, z9.w,
-                             z10.x, z10.y, z10.z, z10.w};
-        float u[6];
-        dw.obs_uniforms(u);
-        float on[13];
-        observe_full(b.pos, b.vel, rpy, wb, bias, lpf, cfg, z, u, on);
-        e.set3(CF_S_GYRO_BIAS, bias); e.set3(CF_S_LPF, lpf);
 #pragma unroll
-        for (int i = 0; i < 13; ++i) { hist[17 + i] = on[i]; e.f(CF_S_OBS_PREV + i, on[i]); }
+        for (int i = 0; i < 13; ++i) hist[17 + i] = on[i];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { hist[13 + i] = h0[i]; hist[30 + i] = h1[i]; }
     } else {
+        // 42-d row without sensor noise: [o(k-1) 13, u(k-1)?..] as the reference's compute_history lays it out for obs 17 + 4
 #pragma unroll
         for (int i = 0; i < 4; ++i) { hist[13 + i] = ap1[i]; hist[17 + i] = h0[i]; hist[38 + i] = h1[i]; hist[34 + i] = a[i]; }
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            hist[21 + i] = b.pos[i]; hist[28 + i] = b.vel[i]; hist[31 + i] = wb[i];
-            e.f(CF_S_OBS_PREV + i, b.pos[i]); e.f(CF_S_OBS_PREV + 7 + i, b.vel[i]); e.f(CF_S_OBS_PREV + 10 + i, wb[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { hist[24 + i] = b.quat[i]; e.f(CF_S_OBS_PREV + 3 + i, b.quat[i]); }
+        for (int i = 0; i < 13; ++i) hist[21 + i] = on[i];
     }
     __syncwarp(wmask);                                      // every lane has read its draws: the rows may overwrite the scratch
     store_row<OD>(row, hist);

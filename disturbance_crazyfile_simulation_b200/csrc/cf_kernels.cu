@@ -65,7 +65,7 @@ __device__ __forceinline__ unsigned smid() { unsigned r; asm volatile("mov.u32 %
 __global__ void k_init(float* __restrict__ S, int n_pad, DevCfg cfg) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
-    init_env(EnvRef{env_global(S, i)}, cfg);
+    init_env(env_ref_global(S, i), cfg);
 }
 
 template <bool NOISE>
@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(128) k_reset(float* __restrict__ S, int n, con
     if (i >= n) return;
     if (mask && !mask[i]) return;
     constexpr int OD = NOISE ? 34 : 42;
-    const EnvRef g{env_global(S, i)};
+    const EnvRef g = env_ref_global(S, i);
     long long gid = cfg.gid_base + i;
     consume_fresh(g, cfg, gid, NOISE);
     uint32_t ctr = g.u(CF_S_RNG_CTR);
@@ -95,18 +95,26 @@ __device__ __forceinline__ void copy_row(float* __restrict__ dst, const float* s
     for (int j = 0; j < OD / 2; ++j) d[j] = s[j];
 }
 
+#ifndef CF_DRAW_UNROLL
+#define CF_DRAW_UNROLL 1                 /* Philox blocks per trip of the step's draw loop */
+#endif
+#ifndef CF_DRAW_HOOK
+#define CF_DRAW_HOOK 6                   /* blocks generated before the loop waits for the state tile */
+#endif
 #ifndef CF_MIN_CTAS
-#define CF_MIN_CTAS (512 / CF_TILE)      /* 512 threads / SM at <= 128 registers: 65 536 envs fit in one wave */
+#define CF_MIN_CTAS (640 / CF_TILE)      /* 5 CTAs = 640 threads / SM: <= 96 registers and <= 44.4 KB of shared memory per CTA */
 #endif
 
 // env.step for all envs, `k` control steps per launch with the tile's state held in shared memory.
-// Timeline of a CTA: (1) thread 0 starts the bulk copy of the state tile; every thread fetches its event
-// counter, action and domain-randomised parameters with ordinary loads and produces ALL standard draws of
-// the step (Philox + Box-Muller, ~40 % of the step's instructions) while the tile is in flight; (2) the step
-// runs against shared memory; (3) envs that finished an episode are reset in place by the whole CTA: up to
-// four at a time, 23 threads per env generate the reset's Philox blocks, then the reset's independent tasks
-// (pose / parameters, the two observations, action history) run on different warps with one env per lane;
-// (4) the tile's state and observation rows leave with one bulk copy each.
+// Timeline of a CTA: (1) thread 0 starts the bulk copy of the tile's 39 staged state words (19.5 KB) and an L2 prefetch of its
+// 21 history words; every thread fetches its event counter, action and domain-randomised parameters with ordinary loads and
+// generates the step's standard draws - ONE rolled loop over the 13 Philox blocks (Box-Muller for the first 11) into
+// shared-memory scratch; after block 5 the loop waits for the tile, issues the HJ sign-table gather and carries on, so the first
+// half of the draws hides the tile's flight and the second half the gather's; (2) the step runs against shared memory, reading
+// and writing the history words straight in HBM; (3) envs that finished an episode are reset in place by the whole CTA: up to
+// four at a time, 23 threads per env generate the reset's Philox blocks, then the reset's independent tasks (pose / parameters,
+// the two observations, action history) run on different warps with one env per lane; (4) the tile's staged words and the
+// observation rows leave with 128-bit coalesced stores.
 template <bool NOISE, int HJ_MODE>
 __global__ void __launch_bounds__(CF_TILE, CF_MIN_CTAS)
 k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, const __grid_constant__ DevTables tab,
@@ -116,14 +124,16 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     constexpr int RC = CF_TILE >= 128 ? 4 : 2;              // finished envs reset concurrently: 23 threads each for the draws + 1
     constexpr bool kParallelReset = NOISE && NW >= 2;
     static_assert(!kParallelReset || 24 * RC <= CF_TILE, "reset groups");
-    constexpr uint32_t kStateBytes = CF_DYN_WORDS * CF_TILE * 4, kObsBytes = OD * CF_TILE * 4;
+    static_assert(RC * 128 <= CF_EXTRA_SLOTS * CF_TILE, "reset scratch aliases the extra draw slots");
+    constexpr uint32_t kStateBytes = CF_BULK_WORDS * CF_TILE * 4, kHistBytes = CF_HIST_WORDS * CF_TILE * 4;
     extern __shared__ __align__(128) float smem[];
-    float* s_state = smem;                                  // [60][CF_TILE]
-    float* s_obs = s_state + CF_DYN_WORDS * CF_TILE;        // [CF_TILE][OD]; before the rows are written: draw scratch
-    float* s_thr = s_obs + OD * CF_TILE;                    // [6][16]
-    float* s_draw = s_thr + 96;                             // [RC][96] reset draws (z[48], u[44]) of the envs being reset
+    float* s_state = smem;                                  // [39][CF_TILE]
+    float* s_obs = s_state + CF_BULK_WORDS * CF_TILE;       // [CF_TILE][OD]; before the rows are written: draw slots 0..31
+    float* s_extra = s_obs + OD * CF_TILE;                  // [12][CF_TILE] draw slots 32..43; after the step phase: reset scratch
+    float* s_draw = s_extra;                                // [RC][96] reset draws (z[48], u[44]) of the envs being reset
     float* s_ctx = s_draw + RC * 96;                        // [RC][32] ResetCtx of the envs being reset
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_ctx + RC * 32);
+    float* s_thr = s_extra + CF_EXTRA_SLOTS * CF_TILE;      // [6][16]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_thr + 96);
     int* s_ndone = reinterpret_cast<int*>(mbar + 1);        // [2]
     uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
     uint32_t* s_hj = reinterpret_cast<uint32_t*>(s_list + CF_TILE);   // [CF_TILE] landing slots of the sign-table gather (cp.async)
@@ -139,72 +149,75 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     const bool bulk_obs = io.bulk_obs && (tile + 1) * CF_TILE <= n;
     unsigned long long* tr = io.trace ? io.trace + CF_TRACE_WORDS * (size_t)tile : nullptr;    // per-CTA timeline (debug)
     if (tr && tid == 0) { tr[0] = smid(); tr[1] = gtimer(); }
-    // the event counter first (the draws wait for it), then the tile: it should not queue behind 15 MB of bulk copies
+    // the event counter first (the draws wait for it), then the tile: it should not queue behind 10 MB of bulk copies
 #ifdef CF_PROBE_NOCTR
     const uint32_t ctr0 = 7u + (uint32_t)k;                 // tools/ only: how much of a CTA's life is the wait for its counter word
 #else
-    const uint32_t ctr0 = __float_as_uint(__ldcg(gtile + CF_S_RNG_CTR * CF_TILE + tid));
+    const uint32_t ctr0 = __float_as_uint(__ldcg(gtile + cf_dev_word(CF_S_RNG_CTR) * CF_TILE + tid));
 #endif
     if (tid == 0) {
         s_ndone[0] = 0;
         mbar_init(mbar, 1);
         mbar_arrive_expect_tx(mbar, kStateBytes);
-#ifdef CF_STAGGER
-        uint32_t z;                                         // the tile is requested once the counter has arrived (counter < 2^31)
-        asm volatile("shr.u32 %0, %1, 31;" : "=r"(z) : "r"(ctr0));
-        bulk_g2s(s_state, gtile + 4 * z, kStateBytes, mbar);
-#else
         bulk_g2s(s_state, gtile, kStateBytes, mbar);
-#endif
+        bulk_prefetch_l2(gtile + CF_BULK_WORDS * CF_TILE, kHistBytes);
     }
-    const EnvRef e{s_state + tid};
-    const EnvRef g{gtile + tid};
-    float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (valid) av = __ldg(reinterpret_cast<const float4*>(io.act) + i);
+    const EnvRef e{s_state + tid, gtile + tid};
+    const EnvRef g{gtile + tid, gtile + tid};
     for (int q = tid; q < 96; q += CF_TILE) s_thr[q] = cfg.hj_thr[q];               // from the constant bank: no global load in front of the HJ lookup
     DrParams p;
     p.load(g);                                              // coalesced loads, in flight with the bulk copy
     const long long gid = cfg.gid_base + i;
     float* row = s_obs + tid * OD;
-    float* scratch = s_obs + warp * (32 * OD) + lane;
     StepDraws sd;
+    sd.s = s_obs + warp * (32 * OD) + lane;
+    sd.x = s_extra + tid;
     if (tr && tid == 0) {
         asm volatile("" :: "r"(ctr0)); tr[12] = gtimer();
     }
-#ifdef CF_BARRIER_FIRST                                       /* tools/ only: A/B against the barrier in front of the draws */
-    __syncthreads();
-#endif
-    DrawSrc dw0 = make_draws(cfg, gid, ctr0, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-    if (valid) pregen_step_draws<NOISE, 0>(dw0, cfg, scratch, sd);   // step event of the launch's first step: counter ctr0, tag 0
-    if (tr && tid == 0) tr[11] = gtimer();
-#ifndef CF_BARRIER_FIRST
-    __syncthreads();                                        // mbarrier initialised, thresholds in place (first needed from here on)
-#endif
-    mbar_wait(mbar, 0);
-    if (tr && tid == 0) tr[2] = gtimer();
-    HjFetch hjf;
-    hjf.raw = 0u; hjf.shift = 0; hjf.slot = nullptr;
-    if (valid) {
-        consume_fresh(e, cfg, gid, NOISE);
-        hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);   // the table gather is in flight behind the second half of the draws
-        pregen_step_draws<NOISE, 1>(dw0, cfg, scratch, sd);
-    }
-    if (tr && tid == 0) tr[13] = gtimer();
     int total_done = 0;
     for (int t = 0; t < k; ++t) {
         const size_t r = (size_t)t * n + i;
         bool my_reset = false;
-        if (valid) {
-            if (t > 0) {
-                av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
-                const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-                hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);
-                pregen_step_draws<NOISE, 0>(dw, cfg, scratch, sd);
-                pregen_step_draws<NOISE, 1>(dw, cfg, scratch, sd);
+        float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) av = __ldg(reinterpret_cast<const float4*>(io.act) + r);
+        HjFetch hjf;
+        hjf.raw = 0u; hjf.shift = 0; hjf.slot = nullptr;
+        // step event of step t: counter ctr0 + t, tag 0.  One rolled loop over the 11 normal blocks keeps the kernel inside the
+        // instruction cache (each unrolled Philox + Box-Muller body is 2.2 KB of code); CF_DRAW_UNROLL blocks per trip.
+        const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
+        {
+            constexpr int U = CF_DRAW_UNROLL, kHook = CF_DRAW_HOOK;
+            static_assert(kHook % U == 0 && kHook < CF_DRAW_BLOCKS, "the tile hook sits at the top of a trip");
+#pragma unroll 1
+            for (int b0 = 0; b0 < CF_DRAW_BLOCKS; b0 += U) {
+                if (b0 == kHook) {
+                    if (t == 0) {
+                        if (tr && tid == 0) tr[11] = gtimer();
+                        __syncthreads();                    // mbarrier initialised, thresholds in place
+                        mbar_wait(mbar, 0);
+                        if (tr && tid == 0) tr[2] = gtimer();
+                        if (valid) consume_fresh(e, cfg, gid, NOISE);
+                    }
+                    // the table gather is in flight behind the second half of the draws
+                    if (valid) hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);
+                }
+                if (valid) {
+                    float4 v[U];
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        if (b0 + u < CF_DRAW_BLOCKS && step_block_live<NOISE>(b0 + u)) v[u] = dw.z(cfg, b0 + u);
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        if (b0 + u < CF_DRAW_BLOCKS && step_block_live<NOISE>(b0 + u)) sd.put(b0 + u, v[u]);
+                }
             }
+        }
+        if (tr && tid == 0 && t == 0) tr[13] = gtimer();
+        if (valid) {
             const float a[4] = {av.x, av.y, av.z, av.w};
             e.u(CF_S_RNG_CTR, ctr0 + (uint32_t)t + 1u);     // an in-place reset in this launch: counter after the step, tag 1
-            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, hjf, a, sd, row, wmask);
+            const StepOut so = step_env<NOISE, HJ_MODE>(e, p, cfg, tab, hjf, a, sd, dw, row, wmask);
             // this warp's table gather has been consumed: HBM may now stream in the inputs of the handle stepped next
             // (cf_set_prefetch_next); each warp asks for a quarter of the CTA's share
             if (io.pf_S && lane == 0 && t == 0) {
@@ -244,7 +257,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                     // R1: the reset events' draws (23 Philox blocks per env, one thread each) + what is read from the old state
                     if (tid < 23 * cnt) {
                         const int j = tid / 23, b = tid - 23 * j, et = s_list[c0 + j];
-                        const EnvRef ee{s_state + et};
+                        const EnvRef ee{s_state + et, gtile + et};
                         const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
                                                       io.inj_reset_u, n, tile * CF_TILE + et, CF_RESET_UNIFORMS);
                         float4 v;
@@ -253,9 +266,9 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         else { v = dr.u(cfg, b - 12); dst = s_draw + j * 96 + CF_RESET_NORMALS + 4 * (b - 12); }
                         dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
                     } else if (tid >= 23 * RC && tid < 23 * RC + cnt) {
-                        const int j = tid - 23 * RC;
+                        const int j = tid - 23 * RC, et = s_list[c0 + j];
                         ResetCtx* c = reinterpret_cast<ResetCtx*>(s_ctx + j * 32);
-                        reset_task_stale(EnvRef{s_state + s_list[c0 + j]}, *c);
+                        reset_task_stale(EnvRef{s_state + et, gtile + et}, *c);
                     }
                     __syncthreads();
                     if (tr && tid == 0 && t == 0 && c0 == 0) tr[14] = gtimer();
@@ -265,13 +278,13 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         const int et = s_list[c0 + lane];
                         const float* zs = s_draw + lane * 96;
                         const float* us = zs + CF_RESET_NORMALS;
-                        const EnvRef ee{s_state + et};
+                        const EnvRef ee{s_state + et, gtile + et};
                         float* rw = s_obs + et * OD;
 #pragma unroll
                         for (int task = 0; task < 4; ++task) {
                             if (warp >= (NW < 4 ? NW : 4) || task % (NW < 4 ? NW : 4) != warp) continue;
                             if (task == 0) reset_task_pose(ee, cfg, zs, us, reinterpret_cast<ResetCtx*>(s_ctx + lane * 32)->wb);
-                            else if (task == 1) reset_task_params(ee, EnvRef{gtile + et}, cfg, us);
+                            else if (task == 1) reset_task_params(ee, EnvRef{gtile + et, gtile + et}, cfg, us);
                             else if (task == 2) reset_task_obs_nongyro<0>(ee, cfg, zs, us, rw);
                             else reset_task_obs_nongyro<1>(ee, cfg, zs, us, rw);
                         }
@@ -281,7 +294,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                     // R3: the gyro samples of both observations (need the new body rate and the old gyro state)
                     if (warp == 0 && lane < cnt) {
                         const int et = s_list[c0 + lane];
-                        reset_task_gyro(EnvRef{s_state + et}, *reinterpret_cast<const ResetCtx*>(s_ctx + lane * 32), cfg,
+                        reset_task_gyro(EnvRef{s_state + et, gtile + et}, *reinterpret_cast<const ResetCtx*>(s_ctx + lane * 32), cfg,
                                         s_draw + lane * 96, s_obs + et * OD);
                     }
                     if (c0 + RC < nd) __syncthreads();      // the scratch is reused by the next group
@@ -289,8 +302,8 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             } else {
                 for (int j = warp; j < nd; j += NW) {       // one env per warp: 23 lanes draw, lane 0 resets
                     const int et = s_list[j];
-                    const EnvRef ee{s_state + et};
-                    const EnvRef gg{gtile + et};
+                    const EnvRef ee{s_state + et, gtile + et};
+                    const EnvRef gg{gtile + et, gtile + et};
                     float* zs = s_draw + (warp % RC) * 96;
                     float* us = zs + CF_RESET_NORMALS;
                     const DrawSrc dr = make_draws(cfg, cfg.gid_base + tile * CF_TILE + et, ee.u(CF_S_RNG_CTR), 1u, io.inj_reset_z,
@@ -314,8 +327,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (my_reset && t + 1 < k) p.load(g);
         }
         if (tr && tid == 0 && t == 0) tr[8] = gtimer();
-#ifndef CF_BULK_TAIL
-        // The tile's rows and state leave with 128-bit stores straight from shared memory (coalesced, conflict-free):
+        // The tile's rows and staged state leave with 128-bit stores straight from shared memory (coalesced, conflict-free):
         // unlike a bulk copy they do not have to be waited for, so the CTA's slot is free as soon as they are issued.
         if (bulk_obs) {
             float4* dst = reinterpret_cast<float4*>(io.obs + ((size_t)t * n + (size_t)tile * CF_TILE) * OD);
@@ -329,26 +341,9 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             float4* dst = reinterpret_cast<float4*>(gtile);
             const float4* src = reinterpret_cast<const float4*>(s_state);
 #pragma unroll
-            for (int j = tid; j < CF_DYN_WORDS * CF_TILE / 4; j += CF_TILE) dst[j] = src[j];
+            for (int j = tid; j < CF_BULK_WORDS * CF_TILE / 4; j += CF_TILE) dst[j] = src[j];
         }
-#else
-        if (bulk_obs) {
-            if (tid == 0) {
-                bulk_s2g(io.obs + ((size_t)t * n + (size_t)tile * CF_TILE) * OD, s_obs, kObsBytes);
-                if (t + 1 == k) bulk_s2g(gtile, s_state, kStateBytes);
-                bulk_commit();
-                bulk_wait_read();                           // shared memory is free again / may be released
-            }
-        } else {
-            if (valid) copy_row<OD>(io.obs + r * OD, row);
-            if (t + 1 == k && tid == 0) {
-                bulk_s2g(gtile, s_state, kStateBytes);
-                bulk_commit();
-                bulk_wait_read();
-            }
-        }
-#endif
-        if (t + 1 < k) __syncthreads();                     // rows may be overwritten by the next step's draws
+        if (t + 1 < k) __syncthreads();                     // rows / extra scratch are overwritten by the next step's draws
     }
     if (tr && tid == 0) { tr[9] = gtimer(); tr[10] = (unsigned long long)total_done; }
 }
@@ -401,18 +396,18 @@ __global__ void k_unpack_state(const float* __restrict__ S, int n, float* __rest
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float* g = env_global(const_cast<float*>(S), i);
-    for (int w = 0; w < CF_STATE_WORDS; ++w) rec[(size_t)i * CF_STATE_WORDS + w] = g[w * CF_TILE];
+    for (int w = 0; w < CF_STATE_WORDS; ++w) rec[(size_t)i * CF_STATE_WORDS + w] = g[cf_dev_word(w) * CF_TILE];
 }
 __global__ void k_pack_state(float* __restrict__ S, int n, const float* __restrict__ rec) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float* g = env_global(S, i);
-    for (int w = 0; w < CF_STATE_WORDS; ++w) g[w * CF_TILE] = rec[(size_t)i * CF_STATE_WORDS + w];
+    for (int w = 0; w < CF_STATE_WORDS; ++w) g[cf_dev_word(w) * CF_TILE] = rec[(size_t)i * CF_STATE_WORDS + w];
 }
 __global__ void k_levels(const float* __restrict__ S, int n, float* __restrict__ out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = (float)misc_level(__float_as_uint(env_global(const_cast<float*>(S), i)[CF_S_MISC * CF_TILE])) / 10.0f;
+    out[i] = (float)misc_level(__float_as_uint(env_global(const_cast<float*>(S), i)[cf_dev_word(CF_S_MISC) * CF_TILE])) / 10.0f;
 }
 
 // PPO GAE (Buffer.finish_path, algs/core.py:498-535; discount_cumsum :105-119), time-major
@@ -440,6 +435,63 @@ __global__ void k_gae(const float* __restrict__ rew, const float* __restrict__ v
         tgt[k] = (float)(run_adv + (double)v);
         disc_ret[k] = (float)run_ret;
         next_val = (double)v;
+    }
+}
+
+// The same scan with four env columns per thread: 128-bit loads and stores (one uchar4 for the flags), four independent
+// recurrences per thread and the loads of the next time steps issued ahead of the arithmetic.  Needs N % 4 == 0 and 16-byte
+// aligned arrays (launch_gae falls back to k_gae otherwise).  Same float64 recurrences, bit-identical results.
+struct GaeLane {
+    double next_val, run_adv, run_ret;
+};
+__device__ __forceinline__ void gae_lane(GaeLane& s, float r, float v, bool d, float ev, bool has_ev, double g, double gl,
+                                         float rew_scale, float& adv, float& tgt, float& ret) {
+    if (d) { s.next_val = has_ev ? (double)ev : 0.0; s.run_adv = 0.0; s.run_ret = s.next_val; }
+    s.run_ret = (double)r + g * s.run_ret;
+    double rs = (double)r;
+    if (rew_scale > 0.0f) rs = (double)fminf(10.0f, fmaxf(-10.0f, __fmul_rn(r, rew_scale)));
+    const double delta = rs + g * s.next_val - (double)v;
+    s.run_adv = delta + gl * s.run_adv;
+    adv = (float)s.run_adv;
+    tgt = (float)(s.run_adv + (double)v);
+    ret = (float)s.run_ret;
+    s.next_val = (double)v;
+}
+__global__ void __launch_bounds__(128) k_gae4(const float4* __restrict__ rew, const float4* __restrict__ val,
+                                              const uchar4* __restrict__ done, const float4* __restrict__ end_val,
+                                              const float4* __restrict__ last_val, float gamma, float lam, float rew_scale, int T,
+                                              int N4, float4* __restrict__ adv, float4* __restrict__ tgt, float4* __restrict__ disc_ret) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N4) return;
+    const double g = (double)gamma, gl = (double)gamma * (double)lam;
+    const float4 lv = last_val[n];
+    GaeLane s[4] = {{(double)lv.x, 0.0, (double)lv.x}, {(double)lv.y, 0.0, (double)lv.y}, {(double)lv.z, 0.0, (double)lv.z},
+                    {(double)lv.w, 0.0, (double)lv.w}};
+    const bool has_ev = end_val != nullptr;
+    constexpr int U = 4;                                    // time steps whose loads are in flight together
+    for (int t0 = T - 1; t0 >= 0; t0 -= U) {
+        float4 r[U], v[U], ev[U];
+        uchar4 d[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 - u;
+            if (t < 0) break;
+            const size_t k = (size_t)t * N4 + n;
+            r[u] = __ldcs(rew + k); v[u] = __ldcs(val + k); d[u] = __ldcs(done + k);
+            ev[u] = has_ev ? __ldcs(end_val + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 - u;
+            if (t < 0) break;
+            const size_t k = (size_t)t * N4 + n;
+            float4 a, tg, rt;
+            gae_lane(s[0], r[u].x, v[u].x, d[u].x != 0, ev[u].x, has_ev, g, gl, rew_scale, a.x, tg.x, rt.x);
+            gae_lane(s[1], r[u].y, v[u].y, d[u].y != 0, ev[u].y, has_ev, g, gl, rew_scale, a.y, tg.y, rt.y);
+            gae_lane(s[2], r[u].z, v[u].z, d[u].z != 0, ev[u].z, has_ev, g, gl, rew_scale, a.z, tg.z, rt.z);
+            gae_lane(s[3], r[u].w, v[u].w, d[u].w != 0, ev[u].w, has_ev, g, gl, rew_scale, a.w, tg.w, rt.w);
+            __stcs(adv + k, a); __stcs(tgt + k, tg); __stcs(disc_ret + k, rt);
+        }
     }
 }
 
@@ -480,6 +532,18 @@ __global__ void k_debug_draws(const __grid_constant__ DevCfg cfg, int first_env,
     reinterpret_cast<uint4*>(words)[t] = w;
     reinterpret_cast<float4*>(draws)[t] = v;
 }
+// quat [n][4] (x, y, z, w) -> the two Euler conversions of a step (quat_to_rpy_bullet, quat2euler_hj), [n][3] each
+__global__ void k_debug_euler(const float4* __restrict__ quat, long long n, float* __restrict__ rpy_bullet, float* __restrict__ rpy_hj) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const float4 v = quat[t];
+    const float q[4] = {v.x, v.y, v.z, v.w};
+    float a[3], b[3];
+    quat_to_rpy_bullet(q, a);
+    quat2euler_hj(q, b);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { rpy_bullet[3 * t + i] = a[i]; rpy_hj[3 * t + i] = b[i]; }
+}
 __global__ void k_debug_box_muller(const uint4* __restrict__ words, long long n, float4* __restrict__ z, float4* __restrict__ u) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -509,8 +573,9 @@ void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float
 }
 
 size_t step_smem_bytes(int obs_dim) {
-    const int rc = CF_TILE >= 128 ? 4 : 2;
-    return (size_t)(CF_DYN_WORDS + obs_dim) * CF_TILE * 4 + 96 * 4 + rc * 96 * 4 + rc * 32 * 4 + 8 + 8 + CF_TILE + CF_TILE * 4;
+    // staged state words + observation rows (= draw slots 0..31) + extra draw slots (= reset scratch) + thresholds + mbarrier +
+    // finished-env counter + list + gather landing slots
+    return (size_t)(CF_BULK_WORDS + obs_dim + CF_EXTRA_SLOTS) * CF_TILE * 4 + 96 * 4 + 8 + 8 + CF_TILE + CF_TILE * 4;
 }
 
 template <bool NOISE, int HJ_MODE>
@@ -562,7 +627,7 @@ __global__ void k_gather_poses(const float* __restrict__ S, int n, const int* __
     if (j >= count) return;
     int i = idx ? idx[j] : j;
     i = min(max(i, 0), n - 1);
-    const EnvRef g{env_global(const_cast<float*>(S), i)};
+    const EnvRef g = env_ref_global(const_cast<float*>(S), i);
 #pragma unroll
     for (int k = 0; k < 3; ++k) poses[7 * j + k] = g.f(CF_S_POS + k);
 #pragma unroll
@@ -577,12 +642,24 @@ void launch_levels(const float* S, int n, float* out, cudaStream_t st) {
 void launch_gae(const float* rew, const float* val, const uint8_t* done, const float* end_val, const float* last_val,
                 float gamma, float lam, float rew_scale, int T, int N, float* adv, float* tgt, float* disc_ret,
                 cudaStream_t st) {
+    const uintptr_t al = (uintptr_t)rew | (uintptr_t)val | (uintptr_t)end_val | (uintptr_t)last_val | (uintptr_t)adv | (uintptr_t)tgt |
+                         (uintptr_t)disc_ret;
+    if (N % 4 == 0 && (al & 15) == 0 && ((uintptr_t)done & 3) == 0) {
+        k_gae4<<<blocks_for(N / 4, 128), 128, 0, st>>>(
+            reinterpret_cast<const float4*>(rew), reinterpret_cast<const float4*>(val), reinterpret_cast<const uchar4*>(done),
+            reinterpret_cast<const float4*>(end_val), reinterpret_cast<const float4*>(last_val), gamma, lam, rew_scale, T, N / 4,
+            reinterpret_cast<float4*>(adv), reinterpret_cast<float4*>(tgt), reinterpret_cast<float4*>(disc_ret));
+        return;
+    }
     k_gae<<<blocks_for(N, 128), 128, 0, st>>>(rew, val, done, end_val, last_val, gamma, lam, rew_scale, T, N, adv, tgt,
                                               disc_ret);
 }
 void launch_debug_draws(const DevCfg& cfg, int first_env, int count, uint32_t ctr, uint32_t tag, int nzb, int nub, uint32_t* words,
                         float* draws, cudaStream_t st) {
     k_debug_draws<<<blocks_for(count * (nzb + nub), 128), 128, 0, st>>>(cfg, first_env, count, ctr, tag, nzb, nub, words, draws);
+}
+void launch_debug_euler(const float* quat, long long n, float* rpy_bullet, float* rpy_hj, cudaStream_t st) {
+    k_debug_euler<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(quat), n, rpy_bullet, rpy_hj);
 }
 void launch_debug_box_muller(const uint32_t* words, long long n, float* z, float* u, cudaStream_t st) {
     k_debug_box_muller<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const uint4*>(words), n,

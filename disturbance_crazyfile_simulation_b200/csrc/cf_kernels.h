@@ -24,7 +24,18 @@ void launch_gae(const float* rew, const float* val, const uint8_t* done, const f
                 cudaStream_t st);
 void launch_debug_draws(const DevCfg& cfg, int first_env, int count, uint32_t ctr, uint32_t tag, int nzb, int nub, uint32_t* words,
                         float* draws, cudaStream_t st);
+void launch_debug_euler(const float* quat, long long n, float* rpy_bullet, float* rpy_hj, cudaStream_t st);
 void launch_debug_box_muller(const uint32_t* words, long long n, float* z, float* u, cudaStream_t st);
+// fused rollout networks (cf_policy.cu): device pointers, torch Linear layout [out][in]
+struct PolicyHostArgs {
+    const float* obs; const float* obs_mean; const float* obs_std;
+    const float* pi_w[3]; const float* pi_b[3]; const float* v_w[3]; const float* v_b[3];
+    const float* log_std; const float* S;
+    float* act; float* val; float* logp;
+    int n, obs_dim, pi_h, v_h, deterministic;
+    float eps;
+};
+cudaError_t launch_policy(const PolicyHostArgs& h, const DevCfg& cfg, cudaStream_t st);
 void set_error(const char* where, const char* what);     // cf_abi.cu: text behind cf_last_error()
 struct PdGains { float hover, kz, kvz, katt, krate, kyaw; };
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st);

@@ -12,6 +12,20 @@
 // words 0..CF_DYN_WORDS-1 change every step (staged through shared memory by the step kernel);
 // the rest are the domain-randomised parameters, rewritten by reset only
 #define CF_DYN_WORDS CF_S_DT
+// Device word order inside a tile (the host-visible record keeps the CF_S_* order of cf_abi.h): the three integer words
+// move in front of the 21 history words (u(k-1), u(k-2), last emitted obs13), so that words 0..CF_BULK_WORDS-1 are what
+// the step kernel stages through shared memory with one bulk copy, and the history words - which a step only copies
+// through into the observation row and overwrites at its very end - stay in global memory (coalesced LDG / STG).
+#define CF_BULK_WORDS 39
+#define CF_HIST_WORDS 21
+#if defined(__CUDACC__)
+#define CF_HD __host__ __device__
+#else
+#define CF_HD
+#endif
+CF_HD constexpr int cf_dev_word(int w) {
+    return w < CF_S_ACT_PREV1 ? w : (w < CF_S_EP_LEN ? w + 3 : (w < CF_S_DT ? w - CF_HIST_WORDS : w));
+}
 // bytes between the packed 2-bit sign tables of consecutive levels (>= ceil(15^6 / 4), 128-B multiple)
 #define CF_SIGN_STRIDE 2847744
 // episode-statistics accumulators are spread over slots (by tile) to avoid same-address atomics
@@ -22,7 +36,10 @@
 namespace cf {
 
 static_assert(CF_DYN_WORDS == 60 && CF_STATE_WORDS == 76, "state record layout");
-static_assert((CF_DYN_WORDS * CF_TILE * 4) % 16 == 0, "bulk copies need 16-byte multiples");
+static_assert((CF_BULK_WORDS * CF_TILE * 4) % 16 == 0 && (CF_HIST_WORDS * CF_TILE * 4) % 16 == 0, "bulk copies need 16-byte multiples");
+static_assert(cf_dev_word(CF_S_ACT_PREV1) == CF_BULK_WORDS && cf_dev_word(CF_S_OBS_PREV + 12) == CF_DYN_WORDS - 1 &&
+              cf_dev_word(CF_S_EP_LEN) == 36 && cf_dev_word(CF_S_MISC) == 38 && CF_BULK_WORDS + CF_HIST_WORDS == CF_DYN_WORDS,
+              "device word order");
 
 // Everything the kernels need from cf_config, pre-derived in float64 on the host (cf_abi.cu).
 struct DevCfg {

@@ -49,9 +49,10 @@ class OnlineMeanStd(nn.Module):
         mean_new = self.mean + delta * n_B / n_AB
         batch_var = du.mean_across_ranks(torch.mean((x - mean_new) ** 2, dim=0))
         M2_AB = n_A * torch.square(self.std) + n_B * batch_var + delta ** 2 * (n_A * n_B / n_AB)
-        self.mean.data = mean_new
-        self.count.data = n_AB
-        self.std.data = torch.sqrt(M2_AB / n_AB)
+        # in place: the fused rollout kernel and captured graphs read these tensors by address
+        self.mean.data.copy_(mean_new)
+        self.count.data.copy_(n_AB)
+        self.std.data.copy_(torch.sqrt(M2_AB / n_AB))
 
 
 def _mlp(sizes, activation) -> nn.Sequential:
@@ -81,7 +82,8 @@ class GaussianActor(nn.Module):
         return (-((act - mu) ** 2) / (2.0 * var) - self.log_std - 0.5 * math.log(2.0 * math.pi)).sum(-1)
 
     def entropy(self) -> torch.Tensor:
-        return (0.5 + 0.5 * math.log(2.0 * math.pi) + self.log_std).sum()
+        """dist.entropy().mean() of the reference (iwpg.py:259): mean over the action dimensions, not their sum."""
+        return (0.5 + 0.5 * math.log(2.0 * math.pi) + self.log_std).mean()
 
 
 class Critic(nn.Module):
@@ -136,7 +138,13 @@ class PPOTrainer:
                  use_reward_scaling: bool = True, use_linear_lr_decay: bool = True,
                  use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
                  target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
-                 gae_fn=None, logger=None, save_freq: int = 10, val_freq: int = 0, val_kwargs: Optional[dict] = None):
+                 gae_fn=None, logger=None, save_freq: int = 10, val_freq: int = 0, val_kwargs: Optional[dict] = None,
+                 fused_rollout: Optional[bool] = None, use_cuda_graphs: Optional[bool] = None):
+        # fused_rollout (default: on for a CUDA CrazyFlieVecEnv): the two networks of ac.step run as ONE kernel per control step
+        # (policy.FusedPolicy / cf_policy_step_dev) that writes straight into the rollout buffers, the env writes its rows
+        # straight into them too (no copies), and the T x 2 launches of a rollout are replayed from one CUDA graph;
+        # use_cuda_graphs also captures one optimiser step of each network (forward, loss, backward, gradient all-reduce,
+        # Adam) and replays it train_pi_iterations / train_v_iterations x num_mini_batches times
         # logger: a run_logger.RunLogger (progress.csv / config.json / torch_save/model{epoch}.pt in the reference's
         # formats, loggers.py:205-513); save_freq as iwpg.py:45,302-304
         # val_freq > 0: validate() every val_freq epochs (iwpg.py:66,297-301; the reference's default is 50); val_kwargs are
@@ -166,7 +174,13 @@ class PPOTrainer:
         self._avg_v = du.FlatGradAverager(list(self.ac.v.parameters()))
         T, N, od = self.T, self.N, env.obs_dim
         f = dict(dtype=torch.float32, device=self.dev)
-        self.obs_buf = torch.empty((T, N, od), **f)
+        on_gpu_env = self.dev.type == 'cuda' and hasattr(env, 'step_into') and hasattr(env, '_h')
+        self.fused = on_gpu_env if fused_rollout is None else bool(fused_rollout)
+        self.use_graphs = (self.dev.type == 'cuda') if use_cuda_graphs is None else bool(use_cuda_graphs)
+        if self.fused and not on_gpu_env:
+            raise ValueError('fused_rollout needs a CUDA CrazyFlieVecEnv')
+        self._obs_all = torch.empty((T + 1, N, od), **f)     # row t: observation the policy sees at step t; row T: after the last step
+        self.obs_buf = self._obs_all[:T]
         self.act_buf = torch.empty((T, N, 4), **f)
         self.rew_buf, self.val_buf, self.logp_buf = torch.empty((T, N), **f), torch.empty((T, N), **f), torch.empty((T, N), **f)
         self.end_val_buf = torch.zeros((T, N), **f)
@@ -174,6 +188,21 @@ class PPOTrainer:
         self.epoch = 0
         self.total_env_steps = 0
         self._obs = None
+        self._fp = self._rollout_graph = self._pi_graph = self._v_graph = None
+        if self.fused:
+            from .policy import FusedPolicy
+            self._fp = FusedPolicy(env, self.ac)
+            self.term_buf = torch.zeros((T, N, od), **f)     # last observation of the envs that finished at step t
+            self.trunc_buf = torch.zeros((T, N), dtype=torch.uint8, device=self.dev)
+            self._scratch_act = torch.empty((N, 4), **f)
+            self._scratch_logp = torch.empty((N,), **f)
+            self.last_val = torch.empty((N,), **f)
+        if self.use_graphs:
+            # Adam with device-side step counters and a tensor learning rate, so that one captured step can be replayed
+            self.pi_optimizer = torch.optim.Adam(self.ac.pi.net.parameters(), lr=torch.tensor(pi_lr, device=self.dev), capturable=True)
+            self.vf_optimizer = torch.optim.Adam(self.ac.v.parameters(), lr=torch.tensor(vf_lr, device=self.dev), capturable=True)
+            self.scheduler = (torch.optim.lr_scheduler.LambdaLR(self.pi_optimizer, lambda e: 1 - e / self.epochs)
+                              if use_linear_lr_decay else None)
         if getattr(env, '_term', None) is None:
             raise ValueError('PPOTrainer needs make(..., return_terminal_obs=True): time-limit cuts bootstrap from V(s_T)')
         if self.logger is not None:                          # logger.save_config(self.params), iwpg.py:126
@@ -188,8 +217,46 @@ class PPOTrainer:
                                          save_freq=save_freq))
 
     # ------------------------------------------------------------------ rollout (iwpg.py:372-410)
+    def _rollout_launches(self) -> None:
+        """The 2 T launches of one rollout: policy kernel (obs row t -> action / value / log-prob row t), step kernel (action
+        row t -> obs row t + 1, reward / done / truncated row t, terminal observations row t)."""
+        env, fp = self.env, self._fp
+        for t in range(self.T):
+            fp.step(self._obs_all[t], self.act_buf[t], self.val_buf[t], self.logp_buf[t])
+            env.step_into(self.act_buf[t], self._obs_all[t + 1], self.rew_buf[t], self.done_buf[t], None, self.term_buf[t],
+                          self.trunc_buf[t])
+        fp.step(self._obs_all[self.T], self._scratch_act, self.last_val, self._scratch_logp, deterministic=True)
+
+    @torch.no_grad()
+    def roll_out_fused(self) -> None:
+        """roll_out with the networks fused into one kernel per step and no copies; from the second epoch on the whole rollout
+        is one CUDA-graph replay.  Paths that end by the time limit bootstrap from V(terminal observation) (iwpg.py:392-397):
+        those rows are rare (an env reaches 500 steps), so they are gathered after the rollout instead of evaluating the value
+        net on every terminal observation of every step."""
+        if self._obs is None:
+            self._obs_all[0].copy_(self.env.reset())
+            self._obs = self._obs_all[0]
+        else:
+            self._obs_all[0].copy_(self._obs_all[self.T])   # paths continue across epochs
+        if self.use_graphs and self.epoch >= 1:
+            if self._rollout_graph is None:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._rollout_launches()
+                self._rollout_graph = g
+            self._rollout_graph.replay()
+        else:
+            self._rollout_launches()
+        idx = self.trunc_buf.nonzero(as_tuple=True)
+        self.end_val_buf.zero_()
+        if idx[0].numel():
+            self.end_val_buf[idx] = self.ac.value(self.term_buf[idx])
+        self.total_env_steps += self.T * self.N * self.world
+
     @torch.no_grad()
     def roll_out(self) -> None:
+        if self.fused:
+            return self.roll_out_fused()
         env, ac = self.env, self.ac
         if self._obs is None:
             self._obs = env.reset()
@@ -236,6 +303,8 @@ class PPOTrainer:
         mbs = B // self.num_mini_batches
         with torch.no_grad():
             info['loss_v_before'] = float(((self.ac.v(obs) - target_v) ** 2).mean())
+        if self.use_graphs:
+            return self._update_graphed(info, raw_obs, obs, act, adv, target_v, logp_old, disc_ret, B, mbs)
         for _ in range(self.train_v_iterations):
             perm = torch.randperm(B, device=self.dev)
             for start in range(0, mbs * self.num_mini_batches, mbs):
@@ -258,9 +327,7 @@ class PPOTrainer:
             self._avg_pi()                                   # mpi_avg_grads(self.ac.pi.net), iwpg.py:458
             self.pi_optimizer.step()
             if self.use_kl_early_stopping:
-                with torch.no_grad():                        # KL(N(mu_old, s) || N(mu_new, s)), same std
-                    kl = (((self.ac.pi.net(obs) - mu_old) ** 2) / (2.0 * torch.exp(2.0 * self.ac.pi.log_std))).sum(-1).mean()
-                if float(du.mean_across_ranks(kl.reshape(1))) > self.target_kl:
+                if self._kl(obs, mu_old) > self.target_kl:
                     stop_iter = i + 1
                     break
         info.update(loss_pi=float(loss_pi.detach()), stop_iter=stop_iter, policy_ratio=float(ratio.detach().mean()))
@@ -269,6 +336,80 @@ class PPOTrainer:
         if self.use_reward_scaling:
             self.ac.ret_oms.update(disc_ret.reshape(-1))
         return info
+
+    def _kl(self, obs, mu_old) -> float:
+        """kl_divergence(p_old, p_new).mean() over all [B, act_dim] elements (iwpg.py:461-466); equal std on both sides."""
+        with torch.no_grad():
+            kl = (((self.ac.pi.net(obs) - mu_old) ** 2) / (2.0 * torch.exp(2.0 * self.ac.pi.log_std))).mean()
+        return float(du.mean_across_ranks(kl.reshape(1)))
+
+    def _update_graphed(self, info, raw_obs, obs, act, adv, target_v, logp_old, disc_ret, B, mbs) -> dict:
+        """The same update with ONE optimiser step of each network captured in a CUDA graph (forward, loss, backward, flattened
+        gradient all-reduce, Adam with device-side step count) and replayed: train_v_iterations x (one graph of num_mini_batches
+        mini-batch steps over a fresh permutation), then train_pi_iterations x the full-batch policy step."""
+        if self._pi_graph is None:
+            # static inputs of the captured steps (the buffers the epoch's data is copied into)
+            self._g_obs = torch.empty_like(obs); self._g_act = torch.empty_like(act); self._g_adv = torch.empty_like(adv)
+            self._g_tgt = torch.empty_like(target_v); self._g_logp = torch.empty_like(logp_old)
+            self._g_perm = torch.randperm(B, device=self.dev)
+        for dst, src in ((self._g_obs, obs), (self._g_act, act), (self._g_adv, adv), (self._g_tgt, target_v), (self._g_logp, logp_old)):
+            dst.copy_(src)
+        if self._pi_graph is None:
+            side = torch.cuda.Stream(self.dev)
+            side.wait_stream(torch.cuda.current_stream(self.dev))
+            with torch.cuda.stream(side):                    # warm-up outside capture (allocator, cuBLAS handles, Adam state)
+                params = [p.detach().clone() for p in self.ac.parameters()]
+                for _ in range(2):
+                    self._v_minibatches(mbs)
+                    self._pi_step()
+                for p, q in zip(self.ac.parameters(), params):
+                    p.data.copy_(q)
+                for opt in (self.pi_optimizer, self.vf_optimizer):      # forget the warm-up steps
+                    for st in opt.state.values():
+                        for v in st.values():
+                            if torch.is_tensor(v):
+                                v.zero_()
+            torch.cuda.current_stream(self.dev).wait_stream(side)
+            self._v_graph, self._pi_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._v_graph):
+                self._v_minibatches(mbs)
+            with torch.cuda.graph(self._pi_graph):
+                self._g_loss_pi, self._g_ratio = self._pi_step()
+        for _ in range(self.train_v_iterations):
+            torch.randperm(B, device=self.dev, out=self._g_perm)
+            self._v_graph.replay()
+        with torch.no_grad():
+            mu_old = self.ac.pi.net(obs) if self.use_kl_early_stopping else None
+        stop_iter = self.train_pi_iterations
+        for i in range(self.train_pi_iterations):
+            self._pi_graph.replay()
+            if i == 0:
+                info['loss_pi_before'] = float(self._g_loss_pi)
+            if self.use_kl_early_stopping and self._kl(obs, mu_old) > self.target_kl:
+                stop_iter = i + 1
+                break
+        info.update(loss_pi=float(self._g_loss_pi), stop_iter=stop_iter, policy_ratio=float(self._g_ratio))
+        self.ac.obs_oms.update(raw_obs)
+        if self.use_reward_scaling:
+            self.ac.ret_oms.update(disc_ret.reshape(-1))
+        return info
+
+    def _v_minibatches(self, mbs: int) -> None:
+        for start in range(0, mbs * self.num_mini_batches, mbs):
+            idx = self._g_perm[start:start + mbs]
+            self.vf_optimizer.zero_grad(set_to_none=False)
+            loss_v = ((self.ac.v(self._g_obs[idx]) - self._g_tgt[idx]) ** 2).mean()
+            loss_v.backward()
+            self._avg_v()
+            self.vf_optimizer.step()
+
+    def _pi_step(self):
+        self.pi_optimizer.zero_grad(set_to_none=False)
+        loss_pi, _, ratio = self.compute_loss_pi(self._g_obs, self._g_act, self._g_adv, self._g_logp)
+        loss_pi.backward()
+        self._avg_pi()
+        self.pi_optimizer.step()
+        return loss_pi.detach(), ratio.detach().mean()
 
     def _sync(self) -> None:
         if self.dev.type == 'cuda':

@@ -171,6 +171,20 @@ class CrazyFlieVecEnv:
             info['terminal_observation'] = self._term
         return self._obs, self._rew, self._done.bool(), info
 
+    def step_into(self, action: torch.Tensor, obs: torch.Tensor, rew: torch.Tensor, done: torch.Tensor,
+                  cost: Optional[torch.Tensor] = None, term_obs: Optional[torch.Tensor] = None,
+                  truncated: Optional[torch.Tensor] = None) -> None:
+        """``step`` writing straight into caller-owned tensors (rows of a rollout buffer): obs [N, obs_dim], rew [N] float32,
+        done / truncated [N] uint8, cost [N]; ``term_obs`` [N, obs_dim] receives the last observation of the envs that finished.
+        No copies, nothing returned; asynchronous on the current stream."""
+        n, od = self.num_envs, self.obs_dim
+        for t, shape, dt in ((action, (n, 4), torch.float32), (obs, (n, od), torch.float32), (rew, (n,), torch.float32),
+                             (done, (n,), torch.uint8)):
+            if t.shape != shape or t.dtype != dt or not t.is_contiguous() or t.device != self.device:
+                raise ValueError(f'step_into: expected contiguous {dt} {shape} on {self.device}, got {t.dtype} {tuple(t.shape)}')
+        abi.check(self._L.cf_step_dev(self._h, _ptr(action), _ptr(obs), _ptr(rew), _ptr(done), _ptr(cost), _ptr(term_obs),
+                                      _ptr(truncated), self._stream()))
+
     def step_k(self, actions: torch.Tensor, obs: Optional[torch.Tensor] = None, rew: Optional[torch.Tensor] = None,
                done: Optional[torch.Tensor] = None, cost: Optional[torch.Tensor] = None):
         """K control steps in one launch (state stays in registers): actions [K, N, 4] ->

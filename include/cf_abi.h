@@ -225,6 +225,31 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
  * (nullable, [n]) receive the return and length of each env's LAST finished episode. */
 int cf_episode_stats(cf_env* env, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host);
 
+/* ---- the rollout's networks, fused -------------------------------------------------------
+ * ActorCritic.step of the reference (algs/core.py:371-394) as IWPGAlgorithm.roll_out calls it once per control step
+ * (algs/iwpg/iwpg.py:372-410), for all envs of a handle in ONE launch: obs_oms(obs) = (obs - mean) / (std + eps)
+ * (utils/online_mean_std.py:32-48), value MLP obs_dim -> v_hidden -> v_hidden -> 1 with tanh (core.py:298-312), policy MLP
+ * obs_dim -> pi_hidden -> pi_hidden -> 4 with relu (core.py:227-260), then a = mu + exp(log_std) * N(0,1) with
+ * logp = sum_j Normal(mu_j, std_j).log_prob(a_j) (core.py:257-266), or a = mu, logp = 1 when `deterministic` (eval mode,
+ * core.py:284-290).  float32 FFMA arithmetic.  All pointers are DEVICE pointers; weight matrices in torch's nn.Linear
+ * layout [out][in] row-major (the tensors of the reference's state_dict: pi.net.{0,2,4}.{weight,bias}, v.net.{0,2,4}.*,
+ * pi.log_std, obs_oms.{mean,std}); obs_mean / obs_std may be NULL (no standardisation).  Hidden widths <= 64.
+ * The exploration noise of env i is Philox4x32-10 keyed by the handle's seed with counter (global env id, the env's event
+ * counter CF_S_RNG_CTR, block 0, tag 4): call it BEFORE the cf_step_* that consumes the actions; results do not depend on
+ * how envs are sharded.  obs [n][obs_dim] (8-byte aligned), act [n][4] (16-byte aligned), val [n], logp [n]; asynchronous
+ * on `stream`. */
+typedef struct cf_policy_weights {
+    const float* obs_mean; const float* obs_std;
+    const float* pi_w[3]; const float* pi_b[3];
+    const float* v_w[3]; const float* v_b[3];
+    const float* log_std;
+    int32_t pi_hidden, v_hidden;
+    float obs_eps;              /* 1e-5, online_mean_std.py:12 */
+    int32_t reserved;
+} cf_policy_weights;
+int cf_policy_step_dev(cf_env* env, const cf_policy_weights* w, const float* obs, int32_t deterministic, float* act, float* val,
+                       float* logp, void* stream);
+
 /* ---- synthetic "PID actions" source of the throughput runs ------------------------------------
  * Attitude -> rate -> motor-mix PD law on the NOISY observation rows (device pointers, asynchronous): structure of
  * the firmware cascade the reference cites (envs/control.py:13-26 gains, :33-50 rpy_control_factors_to_PWM,
@@ -328,6 +353,10 @@ int cf_kernel_timing(cf_env* env, int32_t enable, int32_t reset, double* avg_ms,
 int cf_debug_draws(cf_env* env, int32_t first_env, int32_t count, uint32_t event_ctr, uint32_t tag, int32_t n_norm_blocks,
                    int32_t n_unif_blocks, uint32_t* words_host, float* draws_host);
 int cf_debug_box_muller(int32_t device, const uint32_t* words_host, int64_t n, float* normals_host, float* u01_host);
+/* The two quaternion -> Euler conversions of a step exactly as the kernels compute them (pybullet.getEulerFromQuaternion
+ * of agents.py:446 and quat2euler of distur_gener.py:186-207, both on a polynomial atan2): quat_host [n][4] (x, y, z, w),
+ * outputs [n][3] (roll, pitch, yaw). */
+int cf_debug_euler(int32_t device, const float* quat_host, int64_t n, float* rpy_bullet_host, float* rpy_hj_host);
 
 /* Tracing hook: when `trace_dev` (DEVICE pointer, [cf_num_tiles][16] uint64, caller-owned, zeroed by the caller)
  * is set, every step launch records per tile (times in %globaltimer ns): [0] SM id, [1] CTA start, [2] state tile

@@ -234,7 +234,8 @@ def test_gae_parity():
     import torch
     from disturbance_crazyfile_simulation_b200.gae import gae
     rng = np.random.default_rng(3)
-    for T, N, scale in ((500, 257, 0.0), (64, 4096, 0.37), (1, 3, 0.0)):
+    # N % 4 == 0 takes the four-columns-per-thread kernel (T not a multiple of its unroll too), the others the scalar one
+    for T, N, scale in ((500, 257, 0.0), (64, 4096, 0.37), (1, 3, 0.0), (37, 1028, 0.0), (3, 8, 1.7)):
         rew = (rng.standard_normal((T, N)) - 1.0).astype(np.float32)
         rew[rng.uniform(size=(T, N)) < 0.01] -= 1000.0
         val = rng.standard_normal((T, N)).astype(np.float32)
@@ -245,6 +246,10 @@ def test_gae_parity():
         t = lambda a: torch.tensor(a, device='cuda')
         got = gae(t(rew), t(val), t(done), t(end_val), t(last), 0.99, 0.95, scale)
         for a, b in zip(got, ref):
+            assert rel_err(a.cpu().numpy(), b) < RTOL
+        got2 = gae(t(rew), t(val), t(done), None, t(last), 0.99, 0.95, scale)      # no end values: terminals bootstrap from 0
+        ref2 = co.gae(rew, val, done, None, last, 0.99, 0.95, scale)
+        for a, b in zip(got2, ref2):
             assert rel_err(a.cpu().numpy(), b) < RTOL
 
 
