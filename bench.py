@@ -67,11 +67,13 @@ def parse():
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--graph-passes', type=int, default=4, help='round-robin passes over the shards captured in the CUDA graph')
-    ap.add_argument('--streams', type=int, default=2,
+    ap.add_argument('--streams', type=int, default=4,
                     help='independent shards are stepped on this many streams (parallel branches of the CUDA graph), so one '
                          "shard's load/store phases overlap another's compute")
-    ap.add_argument('--no-prefetch', action='store_true',
-                    help='do not chain the shards with cf_set_prefetch_next (each step kernel asks the L2 to prefetch the next shard)')
+    ap.add_argument('--prefetch', action='store_true',
+                    help='chain the shards with cf_set_prefetch_next (each step kernel asks the L2 to prefetch the next shard): helped the '
+                         'round-1 kernel at 4 CTAs/SM on two streams, measured -2 % with 5 CTAs/SM on four streams (profiles/r2_kstep_ab.json)')
+    ap.add_argument('--no-prefetch', action='store_true', help='(default since round 2; kept for old command lines)')
     ap.add_argument('--workload', default='hover_hj', choices=['hover_hj', 'initial', 'ppo'],
                     help='hover_hj = BASELINE.json configs[2] (the headline); initial = configs[3] (DroneHoverBulletEnvWithAdversaryInitial-v0, '
                          '131072 envs/GPU); ppo = configs[4] (rollout + fused GAE + PPO update, gradient all-reduce)')
@@ -276,7 +278,7 @@ def main_ours(args):
 
     for e in shards:
         e.reset()
-    if not args.no_prefetch and S > 1:
+    if args.prefetch and not args.no_prefetch and S > 1:
         for i in range(S):                               # shard i's step kernel prefetches shard i+1's state and actions into L2
             nxt = i + NS if i + NS < S else i % NS               # the shard this shard's stream steps next
             shards[i].set_prefetch_next(shards[nxt], acts[nxt])
@@ -516,7 +518,7 @@ def main_ours(args):
                        'step_mode': step_mode + (f'; the {S} independent shards alternate over {NS} streams' if NS > 1 else ''),
                        'timing': f'{R} regions of exactly {K} launches each, back to back between one barrier + synchronize pair, each region '
                                  'timed by its own CUDA-event pair; value = median region, max over ranks',
-                       'shard_pipelining': ('off' if args.no_prefetch or S == 1 else
+                       'shard_pipelining': ('off' if not args.prefetch or args.no_prefetch or S == 1 else
                                             'each step kernel issues cp.async.bulk.prefetch.L2 for the state + actions of the shard stepped next '
                                             '(cf_set_prefetch_next); every byte still comes from HBM once per step')},
             'clocks': clocks, 'gpu_launches': int(launches),
@@ -587,6 +589,24 @@ def main_ppo(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dt = float(t.item())
+    # side: the fused network kernel alone (CUDA events, 200 launches on the rollout's last observation rows) against the fp32 FFMA peak
+    pol = {}
+    if getattr(tr, '_fp', None) is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(20):
+            tr._fp.step(tr._obs_all[T], tr._scratch_act, tr.last_val, tr._scratch_logp)
+        ev0.record()
+        for _ in range(200):
+            tr._fp.step(tr._obs_all[T], tr._scratch_act, tr.last_val, tr._scratch_logp)
+        ev1.record(); torch.cuda.synchronize()
+        us = 1e3 * ev0.elapsed_time(ev1) / 200
+        od = env.obs_dim
+        macs = od * 50 + 50 * 50 + 50 * 4 + od * 64 + 64 * 64 + 64            # per env, reference layer sizes
+        peak = 148 * 128 * 2 * 1.965e9
+        pol = {'policy_kernel_us': us, 'policy_kernel_env_steps_per_s': n / (us * 1e-6), 'useful_flop_per_env': 2 * macs,
+               'ffma_frac_of_fp32_peak': 2 * macs * n / (us * 1e-6) / peak, 'fp32_peak_tflops_nominal': peak / 1e12}
+        upd_floor = (80 * 3 * 2 * (od * 50 + 50 * 50 + 50 * 4) + 5 * 3 * 2 * (od * 64 + 64 * 64 + 64)) * n * T / peak
+        pol['update_fp32_ffma_floor_s'] = upd_floor
     if rank == 0:
         roll = sum(i['rollout_s'] for i in infos) / K
         upd = sum(i['update_s'] for i in infos) / K
@@ -598,7 +618,8 @@ def main_ppo(args):
                                    '5x16 value mini-batch steps + 80 full-batch policy steps (reference defaults), one flattened '
                                    'gradient all-reduce per optimiser step', 'envs_per_gpu': n, 'rollout_len': T},
             'side': {'rollout_s_per_epoch': roll, 'update_s_per_epoch': upd, 'rollout_env_steps_per_s': n * T * world / roll,
-                     'EpRet_last': infos[-1]['EpRet'], 'EpLen_last': infos[-1]['EpLen'], 'reference_logged_fps': '129-172 (BASELINE.md)'},
+                     'EpRet_last': infos[-1]['EpRet'], 'EpLen_last': infos[-1]['EpLen'], 'reference_logged_fps': '129-172 (BASELINE.md)',
+                     'fused_rollout': bool(tr.fused), 'cuda_graphs': bool(tr.use_graphs), **pol},
             'gpu_launches': int(env.launch_count)}))
     env.close()
     if world > 1:

@@ -96,6 +96,7 @@ _SIGS = {
     'cf_hj_lookup_host': (C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, _P]),
     'cf_hj_lookup_f32_host': (C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, _P]),
     'cf_episode_stats': (C.c_int, [_P, C.c_int32, _P, _P, _P]),
+    'cf_last_episodes': (C.c_int, [_P, _P, _P, _P]),
     'cf_gae_dev': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P, _P]),
     'cf_gae_host': (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, _P, _P, _P]),
     'cf_set_prefetch_next': (C.c_int, [_P, _P, _P]),

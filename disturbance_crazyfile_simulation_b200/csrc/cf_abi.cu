@@ -715,8 +715,21 @@ int cf_episode_stats(cf_env* e, int32_t reset, double out[4], float* fin_ret_hos
     CU(cudaMemcpy(slots, e->agg, sizeof(slots), cudaMemcpyDeviceToHost));
     for (int k = 0; k < 4; ++k) { out[k] = 0.0; for (int j = 0; j < CF_AGG_SLOTS; ++j) out[k] += slots[4 * j + k]; }
     if (fin_ret_host) CU(cudaMemcpy(fin_ret_host, e->fin_ret, sizeof(float) * (size_t)e->n, cudaMemcpyDeviceToHost));
-    if (fin_len_host) CU(cudaMemcpy(fin_len_host, e->fin_len, sizeof(int) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    if (fin_len_host) {
+        CU(cudaMemcpy(fin_len_host, e->fin_len, sizeof(int) * (size_t)e->n, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < e->n; ++i) fin_len_host[i] &= 0xffff;         // the device word also carries the episode's level index
+    }
     if (reset) CU(cudaMemset(e->agg, 0, sizeof(double) * 4 * CF_AGG_SLOTS));
+    return CF_OK;
+}
+
+int cf_last_episodes(cf_env* e, float* ret_host, int32_t* len_host, float* level_host) {
+    if (!e || !ret_host || !len_host || !level_host) return fail(CF_ERR_INVALID, "cf_last_episodes: null argument%s", "");
+    CU(cudaSetDevice(e->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(ret_host, e->fin_ret, sizeof(float) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(len_host, e->fin_len, sizeof(int) * (size_t)e->n, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < e->n; ++i) { level_host[i] = (float)(len_host[i] >> 16) / 10.0f; len_host[i] &= 0xffff; }
     return CF_OK;
 }
 

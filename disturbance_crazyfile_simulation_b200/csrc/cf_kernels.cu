@@ -233,7 +233,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             if (io.truncated) io.truncated[i] = (uint8_t)so.truncated;
             if (so.done) {
                 io.fin_ret[i] = so.ep_ret;
-                io.fin_len[i] = so.ep_len;
+                io.fin_len[i] = min(so.ep_len, 0xffff) | (misc_level(e.u(CF_S_MISC)) << 16);   // length | level index of the finished episode
                 double* agg = io.agg + 4 * (tile % CF_AGG_SLOTS);
                 atomicAdd(agg + 0, 1.0);
                 atomicAdd(agg + 1, (double)so.ep_ret);

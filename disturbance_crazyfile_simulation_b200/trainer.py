@@ -139,7 +139,7 @@ class PPOTrainer:
                  use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
                  target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
                  gae_fn=None, logger=None, save_freq: int = 10, val_freq: int = 0, val_kwargs: Optional[dict] = None,
-                 fused_rollout: Optional[bool] = None, use_cuda_graphs: Optional[bool] = None):
+                 fused_rollout: Optional[bool] = None, use_cuda_graphs: Optional[bool] = None, episode_rows_per_epoch: int = 256):
         # fused_rollout (default: on for a CUDA CrazyFlieVecEnv): the two networks of ac.step run as ONE kernel per control step
         # (policy.FusedPolicy / cf_policy_step_dev) that writes straight into the rollout buffers, the env writes its rows
         # straight into them too (no copies), and the T x 2 launches of a rollout are replayed from one CUDA graph;
@@ -150,6 +150,7 @@ class PPOTrainer:
         # val_freq > 0: validate() every val_freq epochs (iwpg.py:66,297-301; the reference's default is 50); val_kwargs are
         # passed to validate() (num_evaluations, camera, frame_stride, ...)
         self.val_freq, self.val_kwargs, self._val_env = int(val_freq), dict(val_kwargs or {}), None
+        self.episode_rows_per_epoch, self._episodes_logged = int(episode_rows_per_epoch), 0
         self.logger, self.save_freq, self.seed, self._t_start = logger, int(save_freq), seed, time.time()
         if gae_fn is None:                                   # the fused CUDA kernel; tests of the host logic inject a stand-in
             from .gae import gae as gae_fn
@@ -351,7 +352,7 @@ class PPOTrainer:
             # static inputs of the captured steps (the buffers the epoch's data is copied into)
             self._g_obs = torch.empty_like(obs); self._g_act = torch.empty_like(act); self._g_adv = torch.empty_like(adv)
             self._g_tgt = torch.empty_like(target_v); self._g_logp = torch.empty_like(logp_old)
-            self._g_perm = torch.randperm(B, device=self.dev)
+            self._g_perm = torch.arange(B, device=self.dev)      # refilled from torch.randperm before every replay
         for dst, src in ((self._g_obs, obs), (self._g_act, act), (self._g_adv, adv), (self._g_tgt, target_v), (self._g_logp, logp_old)):
             dst.copy_(src)
         if self._pi_graph is None:
@@ -376,7 +377,7 @@ class PPOTrainer:
             with torch.cuda.graph(self._pi_graph):
                 self._g_loss_pi, self._g_ratio = self._pi_step()
         for _ in range(self.train_v_iterations):
-            torch.randperm(B, device=self.dev, out=self._g_perm)
+            self._g_perm.copy_(torch.randperm(B, device=self.dev))      # same generator use as the eager update
             self._v_graph.replay()
         with torch.no_grad():
             mu_old = self.ac.pi.net(obs) if self.use_kl_early_stopping else None
@@ -440,24 +441,27 @@ class PPOTrainer:
                     FPS=self.T * self.N * self.world / (t2 - t0))
         if self.logger is not None:
             self._log_epoch(info, current_lr)
-        if self.val_freq > 0 and self.epoch % self.val_freq == 0:
+        if self.val_freq > 0 and (self.epoch - 1) % self.val_freq == 0:      # epochs 0, val_freq, ... (iwpg.py:297-301)
             info['validation'] = self.validate(**self.val_kwargs)
         return info
 
     # ------------------------------------------------------------------ validation (iwpg.py:512-568)
     @torch.no_grad()
     def validate(self, num_evaluations: int = 8, capture: bool = True, camera=None, frame_stride: int = 1,
-                 gif_duration_ms: int = 500, max_steps: Optional[int] = None):
+                 gif_duration_ms: int = 500, max_steps: Optional[int] = None, log_penalties: bool = True,
+                 epoch_label: Optional[int] = None):
         """``IWPGAlgorithm.validate`` / ``val_once``: ``num_evaluations`` episodes of the deterministic policy, one row each
         in ``validation_results.csv`` and, with ``capture``, one ``{epoch}-{episode}-{level}.gif`` each under
         ``validation_gifs/`` holding a ``capture_image()`` frame per control step.  The reference runs the episodes one after
         the other on its single env; here they run side by side on a ``num_evaluations``-env twin of the training env
         (same id, same knobs, same HJ tables, no auto-reset) and every step's frames come from one rasteriser launch.
         ``camera`` (raster.make_camera) sets the frame size; default is the reference's 1920x1080.  Rank 0 only, no
-        collective.  The per-step penalty terms the reference writes to ``penalty_data.csv`` are not tracked by the step
-        kernel; that file keeps its header."""
+        collective.  ``log_penalties``: the per-step penalty terms the reference writes to ``penalty_data.csv``
+        (iwpg.py:531-532) are recomputed on the host from the twin env's state after every step (vec_env.penalty_terms)."""
         if self.rank != 0:
             return None
+        # Training_Epoch column / GIF names: the reference's 0-based self.num_epoch of the epoch just finished (iwpg.py:545,562)
+        label = max(self.epoch - 1, 0) if epoch_label is None else int(epoch_label)
         env, k = self.env, int(num_evaluations)
         if self._val_env is None or self._val_env.num_envs != k:
             from .vec_env import CrazyFlieVecEnv
@@ -475,6 +479,7 @@ class PPOTrainer:
         cost = torch.zeros(k, device=self.dev)
         length = torch.zeros(k, dtype=torch.int32, device=self.dev)
         frames = [[] for _ in range(k)]
+        pen_rows = [[] for _ in range(k)]
         limit = int(max_steps or venv._max_episode_steps)
         for t in range(limit):
             if capture and t % frame_stride == 0:
@@ -482,9 +487,16 @@ class PPOTrainer:
                 live = alive.cpu().numpy()
                 for i in range(k):
                     if live[i]:
-                        frames[i].append(img[i])
+                        frames[i].append(img[i].copy())      # a view would pin the whole [k, H, W, 3] batch
             a, _, _ = self.ac.step(o, deterministic=True)
             o, r, d, info = venv.step(a)
+            if log_penalties and self.logger is not None:    # logger.log_penalty(...) per step, iwpg.py:531-532
+                pen = venv.penalty_terms(a.cpu().numpy(), (d & ~info['truncated']).cpu().numpy())
+                live = alive.cpu().numpy()
+                for i in range(k):
+                    if live[i]:
+                        pen_rows[i].append((t + 1, pen['penalty_crash'][i], pen['penalty_rpy'][i], pen['penalty_rpy_dot'][i],
+                                            pen['penalty_z'][i], pen['penalty_velocity'][i], pen['penalty'][i]))
             ret += torch.where(alive, r, torch.zeros_like(r))
             cost += torch.where(alive, info['cost'], torch.zeros_like(r))
             length += alive.to(torch.int32)
@@ -492,17 +504,20 @@ class PPOTrainer:
             if not bool(alive.any()):
                 break
         self.ac.train(was_training)
-        out = dict(epoch=self.epoch, disturbance_level=[float(x) for x in levels], steps=[float(x) for x in length.cpu()],
+        out = dict(epoch=label, disturbance_level=[float(x) for x in levels], steps=[float(x) for x in length.cpu()],
                    returns=[float(x) for x in ret.cpu()], costs=[float(x) for x in cost.cpu()], gifs=[])
         if self.logger is not None:
-            self.logger.log_validation([self.epoch] * k, out['disturbance_level'], out['steps'], out['returns'], out['costs'])
+            self.logger.log_validation([label] * k, out['disturbance_level'], out['steps'], out['returns'], out['costs'])
+            for rows in pen_rows:                            # episode after episode, like the reference's sequential val_once
+                for row in rows:
+                    self.logger.log_penalty(*row)
             if capture:
                 from PIL import Image
                 for i in range(k):
                     if not frames[i]:
                         continue
                     ims = [Image.fromarray(f) for f in frames[i]]
-                    path = f"{self.logger.validation_gifs}/{self.epoch}-{i}-{out['disturbance_level'][i]}.gif"
+                    path = f"{self.logger.validation_gifs}/{label}-{i}-{out['disturbance_level'][i]}.gif"
                     ims[0].save(path, save_all=True, append_images=ims[1:], duration=gif_duration_ms, loop=0)
                     out['gifs'].append(path)
         return out
@@ -510,8 +525,17 @@ class PPOTrainer:
     def _log_epoch(self, info: dict, current_lr: float) -> None:
         """One progress.csv row with the column names of IWPGAlgorithm.log (iwpg.py:309-348) for the quantities the
         batched trainer tracks, then the periodic checkpoint (iwpg.py:302-304).  Episode statistics are the means the
-        step kernel accumulates on the device; per-episode rows (episodic_data.csv) are left to gym-style callers."""
+        step kernel accumulates on the device; episodic_data.csv gets a bounded sample of per-episode rows per epoch."""
         lg = self.logger
+        if self.episode_rows_per_epoch > 0 and hasattr(self.env, 'last_episodes') and self.rank == 0:
+            # episodic_data.csv (loggers.py:612-618; iwpg.py:407-408 writes one row per finished training episode): a bounded
+            # sample per epoch - the last finished episode of the envs that ended one during this rollout
+            ended = self.done_buf.any(dim=0).nonzero().flatten()[: self.episode_rows_per_epoch].cpu().numpy()
+            if ended.size:
+                ret, ln, lv = self.env.last_episodes()
+                lg.log_episodes(self._episodes_logged + 1, [float(round(x, 1)) for x in lv[ended]], [int(x) for x in ln[ended]],
+                                [float(x) for x in ret[ended]])
+                self._episodes_logged += int(ended.size)
         lg.log_tabular('Epoch', info['epoch'])
         lg.log_tabular('EpRet/Mean', float(info['EpRet']))
         lg.log_tabular('EpLen/Mean', float(info['EpLen']))
@@ -531,8 +555,9 @@ class PPOTrainer:
         lg.log_tabular('Time', int(time.time() - self._t_start))
         lg.log_tabular('FPS', int(info['FPS']))
         lg.dump_tabular()
-        if self.epoch % self.save_freq == 0 or self.epoch == self.epochs:
-            lg.torch_save(self.ac.state_dict(), itr=self.epoch)
+        ep0 = self.epoch - 1                                  # 0-based index of the epoch just finished, the reference's self.epoch
+        if ep0 % self.save_freq == 0 or ep0 == self.epochs - 1:   # model0, model{save_freq}, ..., model{epochs-1} (iwpg.py:302-304)
+            lg.torch_save(self.ac.state_dict(), itr=ep0)
 
     def learn(self, epochs: Optional[int] = None, log=None):
         for _ in range(epochs or self.epochs):

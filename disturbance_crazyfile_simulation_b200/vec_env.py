@@ -187,8 +187,10 @@ class CrazyFlieVecEnv:
 
     def step_k(self, actions: torch.Tensor, obs: Optional[torch.Tensor] = None, rew: Optional[torch.Tensor] = None,
                done: Optional[torch.Tensor] = None, cost: Optional[torch.Tensor] = None):
-        """K control steps in one launch (state stays in registers): actions [K, N, 4] ->
-        obs [K, N, obs_dim], rew / done(uint8) / cost [K, N]."""
+        """K control steps in one launch (the tile's state stays on chip): actions [K, N, 4] ->
+        obs [K, N, obs_dim], rew / done(uint8) / cost [K, N].  Open-loop / throughput path: there are no ``truncated`` /
+        ``terminal_observation`` outputs, so with auto-reset a time-limit cut cannot be told from a true terminal - training
+        loops that bootstrap from V(s_T) use :meth:`step` / :meth:`step_into`."""
         act = actions.to(device=self.device, dtype=torch.float32).contiguous()
         k = act.shape[0]
         if act.shape != (k, self.num_envs, 4):
@@ -306,6 +308,15 @@ class CrazyFlieVecEnv:
         return {'episodes': int(n), 'return_sum': out[1], 'length_sum': out[2],
                 'mean_return': out[1] / n if n else float('nan'), 'mean_length': out[2] / n if n else float('nan')}
 
+    def last_episodes(self):
+        """(return [N], length [N], disturbance level [N]) of each env's last finished episode (length 0: none yet) - the
+        columns of the reference's episodic_data.csv (utils/loggers.py:612-618)."""
+        n = self.num_envs
+        ret, ln, lv = np.empty(n, np.float32), np.empty(n, np.int32), np.empty(n, np.float32)
+        abi.check(self._L.cf_last_episodes(self._h, ret.ctypes.data_as(C.c_void_p), ln.ctypes.data_as(C.c_void_p),
+                                           lv.ctypes.data_as(C.c_void_p)))
+        return ret, ln, lv
+
     def set_prefetch_next(self, nxt: Optional['CrazyFlieVecEnv'], next_act: Optional[torch.Tensor] = None) -> None:
         """Shard pipelining hint: while this env is stepped, prefetch the state of ``nxt`` (the env stepped next
         on this GPU) and its action rows into the L2.  Results never depend on it; ``None`` switches it off."""
@@ -338,6 +349,35 @@ class CrazyFlieVecEnv:
 
     def host_sync(self):
         abi.check(self._L.cf_host_sync(self._h))
+
+    # ------------------------------------------------------------------ penalty terms (what the reference logs per step)
+    def penalty_terms(self, action, physical_done, state: Optional[np.ndarray] = None) -> dict:
+        """The terms ``compute_reward`` keeps for logging (hover_free.py:206-235: ``penalty_crash_log``, ``penalty_rpy_log``,
+        ``penalty_rpy_dot_log``, ``penalty_z_log``, ``penalty_velocity_log``, ``penalty_log``; iwpg.py:531-532 writes them to
+        penalty_data.csv per validation step), recomputed on the host from the post-step state record in float64.  The step
+        kernel folds them into the reward; this is the logging path of small validation batches (one ``get_state`` per call).
+        ``action`` [N, 4], ``physical_done`` [N] (done without the time-limit cut)."""
+        F, cfg = abi.STATE_FIELDS, self.cfg
+        st = (self.get_state() if state is None else state).astype(np.float64)
+        g = lambda name: st[:, F[name][0]:F[name][0] + F[name][1]]
+        pos, q, vel, ow = g('pos'), g('quat'), g('vel'), g('omega_w')
+        x, y, z, w = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                      2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                      2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], axis=1).reshape(-1, 3, 3)
+        wb = np.einsum('nji,nj->ni', R, ow)                 # R^T w (agents.py:452-453)
+        sarg = np.clip(-2 * (x * z - w * y), -1, 1)
+        rpy = np.stack([np.arctan2(2 * (y * z + w * x), w * w - x * x - y * y + z * z), np.arcsin(sarg),
+                        np.arctan2(2 * (x * y + w * z), w * w + x * x - y * y - z * z)], axis=1)
+        a = np.asarray(action, np.float64).reshape(-1, 4)
+        out = dict(penalty_rpy=cfg.penalty_angle * np.linalg.norm(rpy, axis=1),
+                   penalty_rpy_dot=cfg.penalty_spin * np.linalg.norm(wb, axis=1),
+                   penalty_velocity=cfg.penalty_velocity * np.linalg.norm(vel, axis=1),
+                   penalty_crash=cfg.penalty_terminal * np.asarray(physical_done, np.float64),
+                   penalty_z=cfg.penalty_z * np.abs(pos[:, 2] - 1.0))
+        p_action = cfg.penalty_action * np.linalg.norm(0.5 * (np.clip(a, -1, 1) + 1), axis=1)
+        out['penalty'] = out['penalty_rpy'] + out['penalty_rpy_dot'] + out['penalty_velocity'] + p_action + out['penalty_crash']
+        return out
 
     def close(self):
         if getattr(self, '_raster', None) is not None:
@@ -392,7 +432,22 @@ class GymAdapter:
         info = {'cost': float(self._cost[0]), 'disturbance_level': self.disturbance_level}
         if self._trunc[0]:
             info['TimeLimit.truncated'] = True
+        self._pen = None
+        self._pen_args = (self._act.copy(), np.array([bool(self._done[0]) and not bool(self._trunc[0])]))
         return self._obs[0].astype(np.float64), float(self._rew[0]), bool(self._done[0]), info
+
+    def _penalty(self, key: str) -> float:
+        """penalty_*_log attributes of the reference env (hover_free.py:229-233), evaluated lazily after a step."""
+        if getattr(self, '_pen', None) is None:
+            self._pen = self.vec.penalty_terms(*self._pen_args)
+        return float(self._pen[key][0])
+
+    penalty_crash_log = property(lambda self: self._penalty('penalty_crash'))
+    penalty_rpy_log = property(lambda self: self._penalty('penalty_rpy'))
+    penalty_rpy_dot_log = property(lambda self: self._penalty('penalty_rpy_dot'))
+    penalty_z_log = property(lambda self: self._penalty('penalty_z'))
+    penalty_velocity_log = property(lambda self: self._penalty('penalty_velocity'))
+    penalty_log = property(lambda self: self._penalty('penalty'))
 
     def render(self, mode='human'):
         return self.vec.render(mode)

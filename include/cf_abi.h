@@ -160,8 +160,12 @@ int cf_reset_dev(cf_env* env, const uint8_t* mask, float* obs, void* stream);
 int cf_step_dev(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
                 float* cost, float* term_obs, uint8_t* truncated, void* stream);
 
-/* k env.step calls in one launch, state kept in registers: act [k][n][4], obs [k][n][obs_dim],
- * rew/done/cost [k][n] (cost may be NULL). */
+/* k env.step calls in one launch, the tile's state kept in shared memory: act [k][n][4], obs [k][n][obs_dim],
+ * rew/done/cost [k][n] (cost may be NULL).  Open-loop / throughput entry: the k action batches must exist up front, and it
+ * has NO truncated / terminal-observation outputs - with auto_reset on, a caller cannot tell time-limit cuts from true
+ * terminals in its [k][n] done flags, so PPO-style bootstrapping from V(s_T) needs cf_step_dev (one step per launch,
+ * `truncated` and `term_obs` outputs).  The last finished episode's return / length per env stay available through
+ * cf_last_episodes. */
 int cf_step_k_dev(cf_env* env, int32_t k, const float* act, float* obs, float* rew,
                   uint8_t* done, float* cost, void* stream);
 
@@ -224,6 +228,10 @@ int cf_gae_host(const float* rew, const float* val, const uint8_t* done, const f
  * on the device since creation or the last call with reset != 0.  fin_ret_host / fin_len_host
  * (nullable, [n]) receive the return and length of each env's LAST finished episode. */
 int cf_episode_stats(cf_env* env, int32_t reset, double out[4], float* fin_ret_host, int32_t* fin_len_host);
+/* One row of the reference's episodic_data.csv per env (utils/loggers.py:612-618: episode, disturbance_level, steps, return):
+ * return, length and disturbance level of each env's LAST finished episode (length 0 = none yet); host arrays [n].  The level is
+ * the one the episode was flown with (hover_free.py:536 draws the next one at the end of reset). */
+int cf_last_episodes(cf_env* env, float* ret_host, int32_t* len_host, float* level_host);
 
 /* ---- the rollout's networks, fused -------------------------------------------------------
  * ActorCritic.step of the reference (algs/core.py:371-394) as IWPGAlgorithm.roll_out calls it once per control step

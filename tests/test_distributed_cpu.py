@@ -151,14 +151,14 @@ def _trainer(rank, world):
     gathered = [torch.zeros_like(w1) for _ in range(world)]
     dist.all_gather(gathered, w1)
     assert torch.equal(gathered[0], gathered[1])
-    # run directory: only rank 0 writes; two epochs -> header + 2 rows, config.json, model2.pt
+    # run directory: only rank 0 writes; two epochs -> header + 2 rows, config.json, model0.pt (the reference's numbering: epochs 0, save_freq, ...)
     import os
     if rank == 0:
         rows = open(os.path.join(log_dir, 'progress.csv')).read().strip().split('\n')
         assert len(rows) == 3 and rows[0].startswith('Epoch,EpRet/Mean,EpLen/Mean,Loss/Pi,Loss/Value')
         assert rows[2].split(',')[0] == '2' and rows[0].split(',')[-3:] == ['TotalEnvSteps', 'Time', 'FPS']
         assert os.path.exists(os.path.join(log_dir, 'config.json'))
-        sd = torch.load(os.path.join(log_dir, 'torch_save', 'model2.pt'))
+        sd = torch.load(os.path.join(log_dir, 'torch_save', 'model0.pt'))
         assert 'pi.net.0.weight' in sd and 'obs_oms.mean' in sd
     else:
         assert os.listdir(log_dir) == []

