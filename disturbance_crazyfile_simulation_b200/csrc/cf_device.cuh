@@ -795,9 +795,22 @@ __device__ __forceinline__ void reset_env(const EnvRef e, const EnvRef g, const 
 #define CF_DRAW_BLOCKS (CF_STEP_NORMALS / 4)   /* 11 Philox blocks */
 #define CF_ROW_SLOTS 32
 #define CF_EXTRA_SLOTS (4 * CF_DRAW_BLOCKS - CF_ROW_SLOTS)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    }
+}
 struct StepDraws {
     float* s;             // s[k * 32]: slot k < 32
     float* x;             // x[(k - 32) * CF_TILE]: slot k >= 32
+    // warp-specialised kernel: the normals are written by producer warps in four stages (blocks 0-1 | 2-4 | 5-6 | 7-10), each
+    // announced on an mbarrier; null in the single-role kernels (the waits fold away)
+    uint64_t* stage_bar;
+    uint32_t stage_parity;
+    __device__ __forceinline__ void wait_stage(int st) const { if (stage_bar) mbar_wait(stage_bar + st, stage_parity); }
     __device__ __forceinline__ float* slot(int k) const { return k < CF_ROW_SLOTS ? s + k * 32 : x + (k - CF_ROW_SLOTS) * CF_TILE; }
     __device__ __forceinline__ void put(int b, float4 v) const {     // b: run-time block index
         float* p = slot(4 * b);
@@ -880,6 +893,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     const float invm = frcp(p.mass);
     float bias[3], lpf[3];
     if (NOISE) { e.get3(CF_S_GYRO_BIAS, bias); e.get3(CF_S_LPF, lpf); }
+    dw.wait_stage(0);
     float4 zq = dw.z<0>();
     const float dmax = ((float)level / 10.0f) * 5.3e-3f;     // distur_gener.py:152,160
     // substeps; the reference calls compute_observation() after each (base.py:494-501): only its
@@ -890,6 +904,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     }
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);             // frame after substep 1: gyro sample and substep 2
     float4 z3;
+    dw.wait_stage(1);
     if (NOISE) {
         float4 z1 = dw.z<1>(), z2 = dw.z<2>();
         z3 = dw.z<3>();
@@ -912,6 +927,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     quat_to_R(b.quat, R); matTvec(R, b.ow, wb);
     float4 z5, z6;
     if (NOISE) {
+        dw.wait_stage(2);
         z5 = dw.z<5>(); z6 = dw.z<6>();
         const float zb[3] = {z4.y, z4.z, z4.w}, zr[3] = {z5.x, z5.y, z5.z}, zt[3] = {z5.w, z6.x, z6.y};
         gyro_update(bias, lpf, cfg, wb, zb, zr, zt);
@@ -931,6 +947,7 @@ __device__ __forceinline__ StepOut step_env(const EnvRef e, const DrParams& p, c
     const bool first = ep_len == 0, second = ep_len == 1;
     float hist[OD], on[13];
     if (NOISE) {
+        dw.wait_stage(3);
         float4 z7 = dw.z<7>(), z8 = dw.z<8>(), z9 = dw.z<9>(), z10 = dw.z<10>();
         const float z[18] = {z6.z, z6.w, z7.x, z7.y, z7.z, z7.w, z8.x, z8.y, z8.z, z8.w, z9.x, z9.y, z9.z, z9.w,
                              z10.x, z10.y, z10.z, z10.w};

@@ -13,23 +13,21 @@
 #include "cf_device.cuh"
 #include "cf_kernels.h"
 
+#include <cstdlib>
+
+#ifndef CF_WS_DEFAULT
+#define CF_WS_DEFAULT 0                  /* 1: the sensor-noise variants launch the warp-specialised kernel (CF_STEP_WS=0/1 overrides at run time) */
+#endif
+
 namespace cf {
 
 // ---------------------------------------------------------------------------------- bulk-copy PTX
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    }
 }
 // global -> shared, completion counted in bytes on the mbarrier (16-byte aligned, 16-byte multiple)
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
@@ -101,6 +99,21 @@ __device__ __forceinline__ void copy_row(float* __restrict__ dst, const float* s
 #ifndef CF_DRAW_HOOK
 #define CF_DRAW_HOOK 6                   /* blocks generated before the loop waits for the state tile */
 #endif
+#ifndef CF_WS_CTAS
+#define CF_WS_CTAS 3                     /* warp-specialised kernel: CTAs of 3 * CF_TILE threads per SM (56 registers per thread at launch) */
+#endif
+#ifndef CF_WS_PRODUCER_REGS
+#define CF_WS_PRODUCER_REGS 40
+#endif
+#ifndef CF_WS_CONSUMER_REGS
+#define CF_WS_CONSUMER_REGS 88           /* 128 x 88 + 256 x 40 = 384 x 56 */
+#endif
+// barrier over the threads that own an env: the whole CTA, or the consumer warps (named barrier 1) of the warp-specialised kernel
+template <bool WS>
+__device__ __forceinline__ void tile_sync() {
+    if (WS) asm volatile("bar.sync 1, %0;" ::"n"(CF_TILE) : "memory");
+    else __syncthreads();
+}
 #ifndef CF_MIN_CTAS
 #define CF_MIN_CTAS (640 / CF_TILE)      /* 5 CTAs = 640 threads / SM: <= 96 registers and <= 44.4 KB of shared memory per CTA */
 #endif
@@ -115,10 +128,18 @@ __device__ __forceinline__ void copy_row(float* __restrict__ dst, const float* s
 // four at a time, 23 threads per env generate the reset's Philox blocks, then the reset's independent tasks (pose / parameters,
 // the two observations, action history) run on different warps with one env per lane; (4) the tile's staged words and the
 // observation rows leave with 128-bit coalesced stores.
-template <bool NOISE, int HJ_MODE>
-__global__ void __launch_bounds__(CF_TILE, CF_MIN_CTAS)
+// WS (warp-specialised, sensor-noise variants only): the CTA has 3 * CF_TILE threads.  Threads CF_TILE.. are PRODUCERS, two per
+// env, that do nothing but generate the step's eleven Philox + Box-Muller blocks (even / odd blocks) into the draw slots and
+// announce them in four stages on mbarriers; threads 0..CF_TILE-1 are the CONSUMERS that run the step as before, minus the draw
+// loop, waiting for a stage where its normals are first read.  Registers follow the roles (setmaxnreg: producers shrink to
+// CF_WS_PRODUCER_REGS, consumers grow to CF_WS_CONSUMER_REGS), so three such CTAs = 36 warps fit an SM.  A launch of 65 536 envs
+// is 2 048 warps of one role in the single-role kernel - 3.5 per scheduler, each a chain of dependent instructions; here the
+// draws (45 % of a CTA's life there) run beside the physics on 6 144 warps.
+template <bool NOISE, int HJ_MODE, bool WS>
+__global__ void __launch_bounds__(WS ? 3 * CF_TILE : CF_TILE, WS ? CF_WS_CTAS : CF_MIN_CTAS)
 k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, const __grid_constant__ DevTables tab,
        const __grid_constant__ StepIO io) {
+    static_assert(!WS || NOISE, "the warp-specialised kernel is built for the sensor-noise variants");
     constexpr int OD = NOISE ? 34 : 42;
     constexpr int NW = CF_TILE / 32;
     constexpr int RC = CF_TILE >= 128 ? 4 : 2;              // finished envs reset concurrently: 23 threads each for the draws + 1
@@ -133,11 +154,36 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     float* s_draw = s_extra;                                // [RC][96] reset draws (z[48], u[44]) of the envs being reset
     float* s_ctx = s_draw + RC * 96;                        // [RC][32] ResetCtx of the envs being reset
     float* s_thr = s_extra + CF_EXTRA_SLOTS * CF_TILE;      // [6][16]
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_thr + 96);
-    int* s_ndone = reinterpret_cast<int*>(mbar + 1);        // [2]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(s_thr + 96);   // [0] state tile landed, [1..4] draw stages (WS)
+    int* s_ndone = reinterpret_cast<int*>(mbar + 5);        // [2]
     uint8_t* s_list = reinterpret_cast<uint8_t*>(s_ndone + 2);   // [CF_TILE] thread ids of finished envs
     uint32_t* s_hj = reinterpret_cast<uint32_t*>(s_list + CF_TILE);   // [CF_TILE] landing slots of the sign-table gather (cp.async)
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x, i = tile * CF_TILE + tid;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, tile = blockIdx.x;
+    if (WS && tid >= CF_TILE) {
+        // ---------------------------------------------------------------- producer warps
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CF_WS_PRODUCER_REGS));
+        const int pe = (tid - CF_TILE) & (CF_TILE - 1), half = (tid - CF_TILE) / CF_TILE, pi = tile * CF_TILE + pe;
+        const float* ptile = S + (size_t)tile * (CF_STATE_WORDS * CF_TILE);
+        const uint32_t pctr = __float_as_uint(__ldcg(ptile + cf_dev_word(CF_S_RNG_CTR) * CF_TILE + pe));
+        StepDraws ps;
+        ps.s = s_obs + (pe >> 5) * (32 * OD) + (pe & 31);
+        ps.x = s_extra + pe;
+        ps.stage_bar = nullptr; ps.stage_parity = 0u;
+        __syncthreads();                                    // the stage barriers are initialised (thread 0)
+        for (int t = 0; t < k; ++t) {
+            const DrawSrc dw = make_draws(cfg, cfg.gid_base + pi, pctr + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, pi, CF_STEP_UNIFORMS);
+#pragma unroll 1
+            for (int b = half; b < CF_DRAW_BLOCKS; b += 2) {
+                if (pi < n) ps.put(b, dw.z(cfg, b));
+                // stages end with blocks 0 | 1, 4 | 3, 6 | 5, 10 | 9 of the even | odd producer: one arrival per thread and stage
+                const int st = b <= 1 ? 0 : (b == 3 || b == 4 ? 1 : (b == 5 || b == 6 ? 2 : (b >= 9 ? 3 : -1)));
+                if (st >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(mbar + 1 + st)) : "memory");
+            }
+            if (t + 1 < k) __syncthreads();                 // the consumers have stored the rows: the slots may be overwritten
+        }
+        return;
+    }
+    const int i = tile * CF_TILE + tid;
 #ifdef CF_GATHER_TO_REGISTER                                  /* tools/ only: A/B against the register-destination gather */
     uint32_t* const my_hj = nullptr;
 #else
@@ -151,13 +197,17 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     if (tr && tid == 0) { tr[0] = smid(); tr[1] = gtimer(); }
     // the event counter first (the draws wait for it), then the tile: it should not queue behind 10 MB of bulk copies
 #ifdef CF_PROBE_NOCTR
-    const uint32_t ctr0 = 7u + (uint32_t)k;                 // tools/ only: how much of a CTA's life is the wait for its counter word
+    uint32_t ctr0 = 7u + (uint32_t)k;                       // tools/ only: how much of a CTA's life is the wait for its counter word
 #else
-    const uint32_t ctr0 = __float_as_uint(__ldcg(gtile + cf_dev_word(CF_S_RNG_CTR) * CF_TILE + tid));
+    uint32_t ctr0 = WS ? 0u : __float_as_uint(__ldcg(gtile + cf_dev_word(CF_S_RNG_CTR) * CF_TILE + tid));   // WS: read from the tile
 #endif
     if (tid == 0) {
         s_ndone[0] = 0;
         mbar_init(mbar, 1);
+        if (WS) {
+#pragma unroll
+            for (int st = 0; st < 4; ++st) mbar_init(mbar + 1 + st, 2 * CF_TILE);
+        }
         mbar_arrive_expect_tx(mbar, kStateBytes);
         bulk_g2s(s_state, gtile, kStateBytes, mbar);
         bulk_prefetch_l2(gtile + CF_BULK_WORDS * CF_TILE, kHistBytes);
@@ -172,6 +222,11 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
     StepDraws sd;
     sd.s = s_obs + warp * (32 * OD) + lane;
     sd.x = s_extra + tid;
+    sd.stage_bar = WS ? mbar + 1 : nullptr; sd.stage_parity = 0u;
+    if (WS) {
+        __syncthreads();                                    // all roles: barriers initialised, thresholds in place
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CF_WS_CONSUMER_REGS));
+    }
     if (tr && tid == 0) {
         asm volatile("" :: "r"(ctr0)); tr[12] = gtimer();
     }
@@ -185,8 +240,18 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         hjf.raw = 0u; hjf.shift = 0; hjf.slot = nullptr;
         // step event of step t: counter ctr0 + t, tag 0.  One rolled loop over the 11 normal blocks keeps the kernel inside the
         // instruction cache (each unrolled Philox + Box-Muller body is 2.2 KB of code); CF_DRAW_UNROLL blocks per trip.
+        if (WS) {
+            if (t == 0) {
+                mbar_wait(mbar, 0);
+                if (tr && tid == 0) tr[2] = gtimer();
+                ctr0 = e.u(CF_S_RNG_CTR);
+                if (valid) consume_fresh(e, cfg, gid, NOISE);
+            }
+            if (valid) hjf = step_issue_hj<HJ_MODE>(e, cfg, tab, s_thr, my_hj);
+            sd.stage_parity = (uint32_t)(t & 1);
+        }
         const DrawSrc dw = make_draws(cfg, gid, ctr0 + (uint32_t)t, 0u, io.inj_step_z, io.inj_step_u, n, i, CF_STEP_UNIFORMS);
-        {
+        if (!WS) {
             constexpr int U = CF_DRAW_UNROLL, kHook = CF_DRAW_HOOK;
             static_assert(kHook % U == 0 && kHook < CF_DRAW_BLOCKS, "the tile hook sits at the top of a trip");
 #pragma unroll 1
@@ -247,7 +312,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         }
         if (tr && t == 0) { __syncwarp(); if (lane == 0) tr[3 + warp] = gtimer(); }
         fence_async_smem();
-        __syncthreads();                                    // step phase of the tile complete, list of finished envs final
+        tile_sync<WS>();                                    // step phase of the tile complete, list of finished envs final
         if (tr && tid == 0 && t == 0) tr[7] = gtimer();
         const int nd = s_ndone[0];
         if (nd > 0) {                                       // uniform over the CTA
@@ -270,7 +335,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         ResetCtx* c = reinterpret_cast<ResetCtx*>(s_ctx + j * 32);
                         reset_task_stale(EnvRef{s_state + et, gtile + et}, *c);
                     }
-                    __syncthreads();
+                    tile_sync<WS>();
                     if (tr && tid == 0 && t == 0 && c0 == 0) tr[14] = gtimer();
                     // R2, one env per lane: pose + motor state (warp 0) | domain randomisation, counters, level (warp 1) |
                     // gyro-free part of the first (warp 2) and second (warp 3) observation + action history
@@ -289,7 +354,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                             else reset_task_obs_nongyro<1>(ee, cfg, zs, us, rw);
                         }
                     }
-                    __syncthreads();
+                    tile_sync<WS>();
                     if (tr && tid == 0 && t == 0 && c0 == 0) tr[15] = gtimer();
                     // R3: the gyro samples of both observations (need the new body rate and the old gyro state)
                     if (warp == 0 && lane < cnt) {
@@ -297,7 +362,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                         reset_task_gyro(EnvRef{s_state + et, gtile + et}, *reinterpret_cast<const ResetCtx*>(s_ctx + lane * 32), cfg,
                                         s_draw + lane * 96, s_obs + et * OD);
                     }
-                    if (c0 + RC < nd) __syncthreads();      // the scratch is reused by the next group
+                    if (c0 + RC < nd) tile_sync<WS>();      // the scratch is reused by the next group
                 }
             } else {
                 for (int j = warp; j < nd; j += NW) {       // one env per warp: 23 lanes draw, lane 0 resets
@@ -322,7 +387,7 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
             }
             total_done += nd;
             fence_async_smem();
-            __syncthreads();                                // resets complete
+            tile_sync<WS>();                                // resets complete
             if (tid == 0) s_ndone[0] = 0;
             if (my_reset && t + 1 < k) p.load(g);
         }
@@ -575,33 +640,38 @@ void launch_reset(float* S, int n, const DevCfg& cfg, const uint8_t* mask, float
 size_t step_smem_bytes(int obs_dim) {
     // staged state words + observation rows (= draw slots 0..31) + extra draw slots (= reset scratch) + thresholds + mbarrier +
     // finished-env counter + list + gather landing slots
-    return (size_t)(CF_BULK_WORDS + obs_dim + CF_EXTRA_SLOTS) * CF_TILE * 4 + 96 * 4 + 8 + 8 + CF_TILE + CF_TILE * 4;
+    return (size_t)(CF_BULK_WORDS + obs_dim + CF_EXTRA_SLOTS) * CF_TILE * 4 + 96 * 4 + 5 * 8 + 8 + CF_TILE + CF_TILE * 4;
 }
 
-template <bool NOISE, int HJ_MODE>
+template <bool NOISE, int HJ_MODE, bool WS>
 static cudaError_t launch_step_variant(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io,
                                        cudaStream_t st) {
-    static bool configured[64] = {};                     // per device: opt in to > 48 KB of dynamic shared memory
+    static bool configured[64] = {};                     // per device and variant: opt in to > 48 KB of dynamic shared memory
     const size_t smem = step_smem_bytes(NOISE ? 34 : 42);
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        cudaError_t err = cudaFuncSetAttribute(k_step<NOISE, HJ_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t err = cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        cudaFuncSetAttribute(k_step<NOISE, HJ_MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         configured[dev] = true;
     }
-    k_step<NOISE, HJ_MODE><<<blocks_for(n, CF_TILE), CF_TILE, smem, st>>>(S, n, k, cfg, tab, io);
+    k_step<NOISE, HJ_MODE, WS><<<blocks_for(n, CF_TILE), WS ? 3 * CF_TILE : CF_TILE, smem, st>>>(S, n, k, cfg, tab, io);
     return cudaSuccess;
 }
 cudaError_t launch_step(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st) {
     const bool sign = cfg.hj_mode == CF_HJ_SIGN_TABLE;
+    static const bool ws = [] { const char* v = getenv("CF_STEP_WS"); return v ? atoi(v) != 0 : (CF_WS_DEFAULT != 0); }();
     if (cfg.obs_noise) {
-        if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE>(S, n, k, cfg, tab, io, st);
-        return launch_step_variant<true, CF_HJ_VALUE_TABLE>(S, n, k, cfg, tab, io, st);
+        if (ws) {
+            if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE, true>(S, n, k, cfg, tab, io, st);
+            return launch_step_variant<true, CF_HJ_VALUE_TABLE, true>(S, n, k, cfg, tab, io, st);
+        }
+        if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE, false>(S, n, k, cfg, tab, io, st);
+        return launch_step_variant<true, CF_HJ_VALUE_TABLE, false>(S, n, k, cfg, tab, io, st);
     }
-    if (sign) return launch_step_variant<false, CF_HJ_SIGN_TABLE>(S, n, k, cfg, tab, io, st);
-    return launch_step_variant<false, CF_HJ_VALUE_TABLE>(S, n, k, cfg, tab, io, st);
+    if (sign) return launch_step_variant<false, CF_HJ_SIGN_TABLE, false>(S, n, k, cfg, tab, io, st);
+    return launch_step_variant<false, CF_HJ_VALUE_TABLE, false>(S, n, k, cfg, tab, io, st);
 }
 void launch_hj_signs(const float* V, uint8_t* P, cudaStream_t st) {
     int nb = (CF_HJ_CELLS + 3) / 4;
