@@ -38,19 +38,25 @@ __device__ __forceinline__ float tanh_fast(float x) {
     return 1.0f - 2.0f * frcp(1.0f + __expf(2.0f * x));
 }
 
-// weights of one layer, torch layout W[out][in] -> Wt[k][j] (k < in rows, 64 columns, columns >= out zero), bias -> bs[64]
+// weights of one layer, torch layout W[out][in] -> Wt[k][j] (k < in rows, 64 columns, columns >= out zero), bias -> bs[64].
+// Asynchronous 4-byte copies (LDGSTS): a thread issues its ~32 elements back to back and waits once - with ordinary loads
+// each element's store waited for its own load (ncu round 2, first build: long scoreboard 22 % of the stall samples, 70 us per
+// launch of which ~45 us were six serialised stagings).  Call stage_wait() + a barrier before the weights are read.
 __device__ __forceinline__ void stage_weights(const float* __restrict__ W, const float* __restrict__ b, int out, int in,
                                               float* Wt, float* bs, int tid) {
+    for (int q = tid; q < out * in; q += kPolTile) {
+        const int j = q / in, k = q - j * in;
+        cp_async_4_nocommit(Wt + k * kWS + j, W + q);
+    }
+    if (tid < out) cp_async_4_nocommit(bs + tid, b + tid);
+    cp_async_commit();
     for (int q = tid; q < in * (kPolMaxH - out); q += kPolTile) {         // zero padding columns
         const int k = q / (kPolMaxH - out), j = out + q % (kPolMaxH - out);
         Wt[k * kWS + j] = 0.0f;
     }
-    for (int q = tid; q < out * in; q += kPolTile) {
-        const int j = q / in, k = q - j * in;
-        Wt[k * kWS + j] = __ldg(W + q);
-    }
-    if (tid < kPolMaxH) bs[tid] = tid < out ? __ldg(b + tid) : 0.0f;
+    if (tid >= out && tid < kPolMaxH) bs[tid] = 0.0f;
 }
+__device__ __forceinline__ void stage_wait() { cp_async_wait_all(); }
 
 // out[j][e] = act(sum_k A[k][e] * Wt[k][j] + b[j]) for the CTA's 128 envs and 64 (padded) neurons.  ACT: 0 relu, 1 tanh.
 template <int ACT>
@@ -105,7 +111,7 @@ __global__ void __launch_bounds__(kPolTile, 2) k_policy(const __grid_constant__ 
         nrm[OD + k] = pa.obs_std ? __fdiv_rn(1.0f, __ldg(pa.obs_std + k) + pa.eps) : 1.0f;
     }
     stage_weights(pa.v_w[0], pa.v_b[0], pa.v_h, OD, Wt, bs, tid);
-    __syncthreads();
+    __syncthreads();                                  // nrm[] in place (the weights are waited for below)
     {   // observation row of this thread's env -> k-major, standardised (online_mean_std.py:32-48)
         const float2* row = reinterpret_cast<const float2*>(pa.obs + (size_t)i * OD);
 #pragma unroll
@@ -115,11 +121,13 @@ __global__ void __launch_bounds__(kPolTile, 2) k_policy(const __grid_constant__ 
             A0[(2 * k2 + 1) * kPolTile + tid] = (v.y - nrm[2 * k2 + 1]) * nrm[OD + 2 * k2 + 1];
         }
     }
+    stage_wait();
     __syncthreads();
     // ---- value net: tanh, tanh, linear (core.py:298-312)
     dense_layer<1>(A0, OD, Wt, bs, A1, pa.v_h, tid);
     __syncthreads();
     stage_weights(pa.v_w[1], pa.v_b[1], pa.v_h, pa.v_h, Wt, bs, tid);
+    stage_wait();
     __syncthreads();
     dense_layer<1>(A1, pa.v_h, Wt, bs, A2, pa.v_h, tid);
     __syncthreads();
@@ -130,10 +138,12 @@ __global__ void __launch_bounds__(kPolTile, 2) k_policy(const __grid_constant__ 
     }
     // ---- policy net: relu, relu, linear (core.py:227-260)
     stage_weights(pa.pi_w[0], pa.pi_b[0], pa.pi_h, OD, Wt, bs, tid);
+    stage_wait();
     __syncthreads();
     dense_layer<0>(A0, OD, Wt, bs, A1, pa.pi_h, tid);
     __syncthreads();
     stage_weights(pa.pi_w[1], pa.pi_b[1], pa.pi_h, pa.pi_h, Wt, bs, tid);
+    stage_wait();
     __syncthreads();
     dense_layer<0>(A1, pa.pi_h, Wt, bs, A2, pa.pi_h, tid);
     __syncthreads();
