@@ -620,10 +620,19 @@ def main_ppo(args):
             'side': {'rollout_s_per_epoch': roll, 'update_s_per_epoch': upd, 'rollout_env_steps_per_s': n * T * world / roll,
                      'EpRet_last': infos[-1]['EpRet'], 'EpLen_last': infos[-1]['EpLen'], 'reference_logged_fps': '129-172 (BASELINE.md)',
                      'fused_rollout': bool(tr.fused), 'cuda_graphs': bool(tr.use_graphs), **pol},
-            'gpu_launches': int(env.launch_count)}))
+            'gpu_launches': int(env.launch_count)}), flush=True)
+    # captured graphs hold the NCCL all-reduce of the optimiser steps: release them before the communicator goes (destroying
+    # the process group under live graphs hung the 2-GPU run of round 2 until its timeout)
+    tr._pi_graph = tr._v_graph = tr._rollout_graph = None
+    del tr
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
     env.close()
     if world > 1:
-        dist.destroy_process_group()
+        dist.barrier()
+        sys.stdout.flush()
+        os._exit(0)                                          # every rank has printed / finished: skip communicator teardown
 
 
 if __name__ == '__main__':
