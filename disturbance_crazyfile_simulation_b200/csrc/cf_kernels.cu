@@ -506,6 +506,12 @@ __global__ void k_gae(const float* __restrict__ rew, const float* __restrict__ v
 // The same scan with four env columns per thread: 128-bit loads and stores (one uchar4 for the flags), four independent
 // recurrences per thread and the loads of the next time steps issued ahead of the arithmetic.  Needs N % 4 == 0 and 16-byte
 // aligned arrays (launch_gae falls back to k_gae otherwise).  Same float64 recurrences, bit-identical results.
+#ifndef CF_GAE_U
+#define CF_GAE_U 2
+#endif
+#ifndef CF_GAE_MIN_CTAS
+#define CF_GAE_MIN_CTAS 7                /* <= 72 registers: N = 524 288 columns (1 024 CTAs) are one wave on 148 SMs */
+#endif
 struct GaeLane {
     double next_val, run_adv, run_ret;
 };
@@ -522,7 +528,7 @@ __device__ __forceinline__ void gae_lane(GaeLane& s, float r, float v, bool d, f
     ret = (float)s.run_ret;
     s.next_val = (double)v;
 }
-__global__ void __launch_bounds__(128) k_gae4(const float4* __restrict__ rew, const float4* __restrict__ val,
+__global__ void __launch_bounds__(128, CF_GAE_MIN_CTAS) k_gae4(const float4* __restrict__ rew, const float4* __restrict__ val,
                                               const uchar4* __restrict__ done, const float4* __restrict__ end_val,
                                               const float4* __restrict__ last_val, float gamma, float lam, float rew_scale, int T,
                                               int N4, float4* __restrict__ adv, float4* __restrict__ tgt, float4* __restrict__ disc_ret) {
@@ -533,7 +539,7 @@ __global__ void __launch_bounds__(128) k_gae4(const float4* __restrict__ rew, co
     GaeLane s[4] = {{(double)lv.x, 0.0, (double)lv.x}, {(double)lv.y, 0.0, (double)lv.y}, {(double)lv.z, 0.0, (double)lv.z},
                     {(double)lv.w, 0.0, (double)lv.w}};
     const bool has_ev = end_val != nullptr;
-    constexpr int U = 4;                                    // time steps whose loads are in flight together
+    constexpr int U = CF_GAE_U;                             // time steps whose loads are in flight together
     for (int t0 = T - 1; t0 >= 0; t0 -= U) {
         float4 r[U], v[U], ev[U];
         uchar4 d[U];

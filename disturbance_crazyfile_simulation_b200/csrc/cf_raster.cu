@@ -38,6 +38,9 @@ struct cf_raster {
     int ctx_frames = 0;
     void* rec = nullptr;         // [rec_frames][n_tris] TriRec + [rec_frames][n_tris] float4 boxes, written by k_tri_setup
     int rec_frames = 0;
+    // the drone pass (k_tri_setup, k_raster) runs on a side stream beside k_background: the two write disjoint pixel blocks
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_ctx = nullptr, ev_done = nullptr;
 };
 
 namespace {
@@ -61,13 +64,17 @@ struct FrameCtx {
     uint32_t bg, ga, gb;         // packed colours: background, the two ground squares (already shaded)
     float ihw, ihh;              // 2 / width, 2 / height
     int bx0, bx1, by0, by1;      // pixel bounds of the triangles that survive set-up (k_tri_setup: atomicMin / atomicMax)
+    int wx, wy;                  // first block of the drone window (bounded mode): floor((cx - rad) / 32), floor((cy - rad) / 8)
+    int dx0, dx1, dy0, dy1;      // 32 x 8 pixel blocks [dx0, dx1] x [dy0, dy1] that belong to the drone pass (empty: dx0 > dx1)
 };
+constexpr int RW = 32, RH = 8;
+struct DroneWin { int on, bounded, gx, gy; };
 
 struct TriRec { float4 a, b, c; };   // (x0 y0 x1 y1) (x2 y2 1/area 1/z0) (1/z1 1/z2 rgb idx)
 
 // one thread per frame: everything that depends on the pose only
 __global__ void k_frame_ctx(const __grid_constant__ cf_camera cam, float radius, const float* __restrict__ poses, int n_frames,
-                            FrameCtx* __restrict__ ctx) {
+                            const DroneWin win, FrameCtx* __restrict__ ctx) {
     const int frame = blockIdx.x * blockDim.x + threadIdx.x;
     if (frame >= n_frames) return;
     FrameCtx fc;
@@ -101,6 +108,23 @@ __global__ void k_frame_ctx(const __grid_constant__ cf_camera cam, float radius,
     fc.ihh = D(2.f, (float)cam.height);
     fc.bx0 = fc.by0 = 0x7fffffff;
     fc.bx1 = fc.by1 = -0x7fffffff - 1;
+    // Blocks of the drone pass: k_raster rewrites exactly these whole, k_background leaves exactly these alone, so the two run
+    // side by side.  The blocks the screen bound of the bounding sphere touches plus one block of slack on every side, cut to
+    // the window of blocks k_raster is launched over (bounded mode) and to the frame.
+    const int nbx = (cam.width + RW - 1) / RW, nby = (cam.height + RH - 1) / RH;
+    fc.wx = (int)floorf((fc.cx - fc.rad) / (float)RW);
+    fc.wy = (int)floorf((fc.cy - fc.rad) / (float)RH);
+    int x0 = 0, x1 = nbx - 1, y0 = 0, y1 = nby - 1;
+    if (fc.rad >= 0.f) {
+        x0 = max(x0, (int)floorf((fc.cx - fc.rad) / (float)RW) - 1); x1 = min(x1, (int)floorf((fc.cx + fc.rad) / (float)RW) + 1);
+        y0 = max(y0, (int)floorf((fc.cy - fc.rad) / (float)RH) - 1); y1 = min(y1, (int)floorf((fc.cy + fc.rad) / (float)RH) + 1);
+    }
+    if (win.bounded) {
+        x0 = max(x0, fc.wx); x1 = min(x1, fc.wx + win.gx - 1);
+        y0 = max(y0, fc.wy); y1 = min(y1, fc.wy + win.gy - 1);
+    }
+    if (!win.on) { x0 = 1; x1 = 0; }
+    fc.dx0 = x0; fc.dx1 = x1; fc.dy0 = y0; fc.dy1 = y1;
     ctx[frame] = fc;
 }
 
@@ -117,6 +141,8 @@ __global__ void __launch_bounds__(NT) k_background(const __grid_constant__ cf_ca
     const int W = cam.width, H = cam.height;
     if (px0 >= W) return;
     const FrameCtx* c = ctx + frame;
+    const int dy0 = __ldg(&c->dy0), dy1 = __ldg(&c->dy1);
+    const bool in_cols = (px0 >> 5) >= __ldg(&c->dx0) && (px0 >> 5) <= __ldg(&c->dx1);
     const float ex = keep(__ldg(&c->eye[0])), ey = keep(__ldg(&c->eye[1])), ez = __ldg(&c->eye[2]);
     const float ihw = __ldg(&c->ihw), ihh = __ldg(&c->ihh);
     const uint32_t bg = __ldg(&c->bg), ga = __ldg(&c->ga), gb = __ldg(&c->gb);
@@ -135,6 +161,7 @@ __global__ void __launch_bounds__(NT) k_background(const __grid_constant__ cf_ca
     for (int r = 0; r < GROWS; ++r) {
         const int py = by0 + ty + BH * r;
         if (py >= H) break;
+        if (in_cols && (py >> 3) >= dy0 && (py >> 3) <= dy1) continue;   // the drone pass (k_raster) writes this 32 x 8 block
         const float tyv = M(Sb(1.f, M(A((float)py, 0.5f), ihh)), cam.tan_y);
         const float cxr = A(cam.fwd[0], M(cam.up[0], tyv)), cyr = A(cam.fwd[1], M(cam.up[1], tyv)), czr = A(cam.fwd[2], M(cam.up[2], tyv));
         uint32_t col[4] = {bg, bg, bg, bg};
@@ -246,9 +273,8 @@ __global__ void __launch_bounds__(NT) k_tri_setup(const float* __restrict__ tris
 // frame's bounding boxes 32 at a time (one per lane) and walks only the triangles that reach its patch.
 // bounded != 0: the grid is a window of blocks hung at the sphere's screen bound (follow cameras, where the host knows its
 // size); else the grid covers the frame and untouched CTAs leave at once.
-constexpr int RW = 32, RH = 8;
 __global__ void __launch_bounds__(NT) k_raster(int n_tris, const __grid_constant__ cf_camera cam, const FrameCtx* __restrict__ ctx,
-                                               const TriRec* __restrict__ rec, const float4* __restrict__ bbs, int bounded,
+                                               const TriRec* __restrict__ rec, const float4* __restrict__ bbs, const DroneWin win,
                                                uint8_t* __restrict__ out) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wx0 = 8 * (warp & 3), wy0 = 4 * (warp >> 2);
@@ -256,20 +282,11 @@ __global__ void __launch_bounds__(NT) k_raster(int n_tris, const __grid_constant
     const int W = cam.width, H = cam.height;
     const FrameCtx* c = ctx + frame;
     int tbx = blockIdx.x, tby = blockIdx.y;
-    {
-        const float bcx = __ldg(&c->cx), bcy = __ldg(&c->cy), brad = __ldg(&c->rad);
-        if (bounded) {
-            tbx += (int)floorf((bcx - brad) / (float)RW);
-            tby += (int)floorf((bcy - brad) / (float)RH);
-            if (tbx < 0 || tby < 0 || tbx * RW >= W || tby * RH >= H) return;
-        }
-        const float fx0 = (float)(tbx * RW), fy0 = (float)(tby * RH);
-        if (!(brad < 0.f || (fx0 <= bcx + brad && fx0 + (float)RW >= bcx - brad && fy0 <= bcy + brad && fy0 + (float)RH >= bcy - brad)))
-            return;
-    }
-    // the pixel bounds k_tri_setup found (one pixel of slack): blocks outside leave, patches outside skip the scan
+    if (win.bounded) { tbx += __ldg(&c->wx); tby += __ldg(&c->wy); }
+    if (tbx < __ldg(&c->dx0) || tbx > __ldg(&c->dx1) || tby < __ldg(&c->dy0) || tby > __ldg(&c->dy1)) return;   // k_background's block
+    // the pixel bounds k_tri_setup found (one pixel of slack): a block or patch outside them skips the triangle scan and
+    // writes the background only (it still writes: k_background left the block alone)
     const int qx0 = c->bx0 - 1, qx1 = c->bx1 + 1, qy0 = c->by0 - 1, qy1 = c->by1 + 1;
-    if (tbx * RW > qx1 || tbx * RW + RW < qx0 || tby * RH > qy1 || tby * RH + RH < qy0) return;
     const bool live = !(tbx * RW + wx0 > qx1 || tbx * RW + wx0 + 8 < qx0 || tby * RH + wy0 > qy1 || tby * RH + wy0 + 4 < qy0);
     const int px = tbx * RW + wx0 + (lane & 7), py = tby * RH + wy0 + (lane >> 3);
 
@@ -362,6 +379,12 @@ int cf_raster_create(cf_raster** out, int32_t device, const float* tris_host, co
         cf_raster_destroy(r);
         return fail(CF_ERR_ALLOC, "cf_raster_create", "out of device memory");
     }
+    if (cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->ev_ctx, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming) != cudaSuccess) {
+        cf_raster_destroy(r);
+        return fail(CF_ERR_CUDA, "cf_raster_create", "could not create the side stream");
+    }
     if (n_tris > 0) {
         RCU(cudaMemcpy(r->tris, tris_host, (size_t)n_tris * 9 * sizeof(float), cudaMemcpyHostToDevice));
         RCU(cudaMemcpy(r->rgb, rgb_host, (size_t)n_tris * 3 * sizeof(float), cudaMemcpyHostToDevice));
@@ -377,6 +400,9 @@ void cf_raster_destroy(cf_raster* r) {
     cudaFree(r->rgb);
     cudaFree(r->ctx);
     cudaFree(r->rec);
+    if (r->ev_ctx) cudaEventDestroy(r->ev_ctx);
+    if (r->ev_done) cudaEventDestroy(r->ev_done);
+    if (r->side) cudaStreamDestroy(r->side);
     delete r;
 }
 
@@ -424,15 +450,20 @@ int cf_raster_render_dev(cf_raster* r, const cf_camera* cam, const float* poses_
     for (int f0 = 0; f0 < n_frames; f0 += batch) {
         const int nf = n_frames - f0 < batch ? n_frames - f0 : batch;
         uint8_t* o = rgb_dev + (size_t)f0 * cam->height * cam->width * 3;
-        k_frame_ctx<<<(nf + 127) / 128, 128, 0, st>>>(*cam, r->radius, poses_dev + 7 * (size_t)f0, nf, ctx);
+        const DroneWin win{r->n_tris > 0 ? 1 : 0, bounded, (int)grid.x, (int)grid.y};
+        k_frame_ctx<<<(nf + 127) / 128, 128, 0, st>>>(*cam, r->radius, poses_dev + 7 * (size_t)f0, nf, win, ctx);
+        if (r->n_tris > 0) {                                // drone pass on the side stream, beside the background pass
+            RCU(cudaEventRecord(r->ev_ctx, st));
+            RCU(cudaStreamWaitEvent(r->side, r->ev_ctx, 0));
+            k_tri_setup<<<dim3((r->n_tris + NT - 1) / NT, nf), NT, 0, r->side>>>(r->tris, r->rgb, r->n_tris, *cam, ctx, rec, bbs);
+            grid.z = nf;
+            k_raster<<<grid, NT, 0, r->side>>>(r->n_tris, *cam, ctx, rec, bbs, win, o);
+            RCU(cudaEventRecord(r->ev_done, r->side));
+        }
         dim3 gbg((cam->width + BW - 1) / BW, (cam->height + GH - 1) / GH, nf);
         if (cam->right[2] == 0.f) k_background<true><<<gbg, NT, 0, st>>>(*cam, ctx, o);
         else k_background<false><<<gbg, NT, 0, st>>>(*cam, ctx, o);
-        if (r->n_tris > 0) {
-            k_tri_setup<<<dim3((r->n_tris + NT - 1) / NT, nf), NT, 0, st>>>(r->tris, r->rgb, r->n_tris, *cam, ctx, rec, bbs);
-            grid.z = nf;
-            k_raster<<<grid, NT, 0, st>>>(r->n_tris, *cam, ctx, rec, bbs, bounded, o);
-        }
+        if (r->n_tris > 0) RCU(cudaStreamWaitEvent(st, r->ev_done, 0));
     }
     RCU(cudaGetLastError());
     return CF_OK;
