@@ -61,13 +61,13 @@ def parse():
     ap.add_argument('--warmup', type=int, default=200)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--envs', type=int, default=65536, help='envs per GPU per step')
-    ap.add_argument('--shards', type=int, default=8, help='independent env shards per GPU (L2 eviction)')
+    ap.add_argument('--shards', type=int, default=16, help='independent env shards per GPU (L2 eviction; every shard is its own handle)')
     ap.add_argument('--kfuse', type=int, default=32, help='control steps per launch in the fused side measurement')
     ap.add_argument('--e2e-steps', type=int, default=200)
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--graph-passes', type=int, default=4, help='round-robin passes over the shards captured in the CUDA graph')
-    ap.add_argument('--streams', type=int, default=4,
+    ap.add_argument('--streams', type=int, default=16,
                     help='independent shards are stepped on this many streams (parallel branches of the CUDA graph), so one '
                          "shard's load/store phases overlap another's compute")
     ap.add_argument('--prefetch', action='store_true',
@@ -365,7 +365,8 @@ def main_ours(args):
     t1 = time.time()
     regions = [evs[r].elapsed_time(evs[r + 1]) for r in range(R)]
     ms = statistics.median(regions)
-    launches = K * (2 if PD else 1)                      # one k_step launch per control step (graph nodes included) [+ k_pd_actions]
+    deferred = os.environ.get('CF_DEFER_RESET', '1') != '0'   # single-step launches: k_step + k_reset_list (the in-place resets of the step)
+    launches = K * ((2 if PD else 1) + (1 if deferred else 0))   # graph nodes per control step: k_step [+ k_reset_list] [+ k_pd_actions]
     clocks = sampler.stop(t0, t1) if sampler else None
     kern_ms = ms / K                                     # launch-to-launch time of the dominant kernel inside the timed region
     t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)

@@ -60,6 +60,8 @@ struct cf_env {
     float* fin_ret = nullptr;
     int* fin_len = nullptr;
     double* agg = nullptr;
+    int* reset_list = nullptr;       // deferred resets of single-step launches: [n] env indices + [2] counters (cf_types.h StepIO)
+    int* reset_count = nullptr;
     float* rec_dev = nullptr;        // scratch for get/set_state
     // host-pointer API: private stream + device mirrors of the caller's host buffers
     cudaStream_t hstream = nullptr;
@@ -295,6 +297,7 @@ int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint
     io.term_obs = term_obs; io.truncated = truncated;
     io.inj_step_z = e->inj[0]; io.inj_step_u = e->inj[1]; io.inj_reset_z = e->inj[2]; io.inj_reset_u = e->inj[3];
     io.fin_ret = e->fin_ret; io.fin_len = e->fin_len; io.agg = e->agg;
+    io.reset_list = e->reset_list; io.reset_count = e->reset_count;
     // a full tile's observation rows leave with one bulk copy when every tile's first row is 16-byte aligned
     io.trace = e->trace;
     io.pf_S = e->pf_next ? e->pf_next->S : nullptr; io.pf_act = e->pf_next ? e->pf_act : nullptr;
@@ -309,7 +312,7 @@ int step_common(cf_env* e, int k, const float* act, float* obs, float* rew, uint
     cudaError_t lerr = launch_step(e->S, e->n, k, e->dev, e->tab, io, st);
     end_timing(ep, st);
     if (lerr != cudaSuccess) return cuda_fail(lerr, "launch_step");
-    e->launches += 1;
+    e->launches += (k == 1 && e->dev.auto_reset) ? 2 : 1;    // the step kernel + the list-driven reset kernel of single-step launches
     CU(cudaGetLastError());
     return CF_OK;
 }
@@ -385,6 +388,9 @@ int cf_create(const cf_config* cfg, int32_t n_envs, int32_t device, uint64_t see
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_ret, sizeof(float) * (size_t)n_envs);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->fin_len, sizeof(int) * (size_t)n_envs);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->agg, sizeof(double) * 4 * CF_AGG_SLOTS);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->reset_list, sizeof(int) * (size_t)n_envs);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&e->reset_count, sizeof(int) * 2);
+    if (err == cudaSuccess) err = cudaMemset(e->reset_count, 0, sizeof(int) * 2);
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->thr_dev, sizeof(thr));
     if (err == cudaSuccess) err = cudaMalloc((void**)&e->value_ptrs_dev, sizeof(float*) * CF_MAX_LEVELS);
     if (err == cudaSuccess && hj) err = cudaMalloc((void**)&e->signs_slab, (size_t)CF_SIGN_STRIDE * CF_MAX_LEVELS);
@@ -409,7 +415,7 @@ int cf_destroy(cf_env* e) {
     for (int i = 0; i < CF_MAX_LEVELS; ++i) cudaFree(e->value_dev[i]);
     cudaFree(e->signs_slab); cudaFree((void*)e->value_ptrs_dev); cudaFree(e->thr_dev);
     for (int i = 0; i < 4; ++i) cudaFree(e->inj[i]);
-    cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
+    cudaFree(e->reset_list); cudaFree(e->reset_count); cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
     cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
     cudaFree(e->d_done); cudaFree(e->d_trunc); cudaFree(e->d_mask);
     for (EventPair& p : e->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }

@@ -135,7 +135,12 @@ __device__ __forceinline__ void tile_sync() {
 // CF_WS_PRODUCER_REGS, consumers grow to CF_WS_CONSUMER_REGS), so three such CTAs = 36 warps fit an SM.  A launch of 65 536 envs
 // is 2 048 warps of one role in the single-role kernel - 3.5 per scheduler, each a chain of dependent instructions; here the
 // draws (45 % of a CTA's life there) run beside the physics on 6 144 warps.
-template <bool NOISE, int HJ_MODE, bool WS>
+// INRESET: finished envs are reset in place by the CTA (needed when k > 1: the episode continues inside the launch).  Without
+// it (single-step launches) the step kernel only appends the env to a list and the reset is done by k_reset_list behind it on
+// the same stream: the reset is a 2.3 us latency chain that 63 % of the tiles of a 65 536-env step ran with 126 of 128 threads
+// idle (21 % of the sustained step time, measured on one launch of 524 288 envs with and without finished episodes), and its
+// code is a quarter of the kernel; in the list kernel a warp owns a finished env and other streams' step kernels fill the SMs.
+template <bool NOISE, int HJ_MODE, bool WS, bool INRESET>
 __global__ void __launch_bounds__(WS ? 3 * CF_TILE : CF_TILE, WS ? CF_WS_CTAS : CF_MIN_CTAS)
 k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, const __grid_constant__ DevTables tab,
        const __grid_constant__ StepIO io) {
@@ -305,8 +310,12 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
                 atomicAdd(agg + 2, (double)so.ep_len);
                 if (cfg.auto_reset) {
                     if (io.term_obs) copy_row<OD>(io.term_obs + (size_t)i * OD, row);
-                    s_list[atomicAdd(s_ndone, 1)] = (uint8_t)tid;
-                    my_reset = true;
+                    if (INRESET) {
+                        s_list[atomicAdd(s_ndone, 1)] = (uint8_t)tid;
+                        my_reset = true;
+                    } else {
+                        io.reset_list[atomicAdd(io.reset_count, 1)] = i;
+                    }
                 }
             }
         }
@@ -314,8 +323,8 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         fence_async_smem();
         tile_sync<WS>();                                    // step phase of the tile complete, list of finished envs final
         if (tr && tid == 0 && t == 0) tr[7] = gtimer();
-        const int nd = s_ndone[0];
-        if (nd > 0) {                                       // uniform over the CTA
+        const int nd = INRESET ? s_ndone[0] : 0;
+        if (INRESET && nd > 0) {                            // uniform over the CTA
             if (kParallelReset) {
                 for (int c0 = 0; c0 < nd; c0 += RC) {
                     const int cnt = min(RC, nd - c0);
@@ -411,6 +420,42 @@ k_step(float* __restrict__ S, int n, int k, const __grid_constant__ DevCfg cfg, 
         if (t + 1 < k) __syncthreads();                     // rows / extra scratch are overwritten by the next step's draws
     }
     if (tr && tid == 0) { tr[9] = gtimer(); tr[10] = (unsigned long long)total_done; }
+}
+
+// Deferred in-place resets of a single-step launch: one WARP per finished env (grid-stride over the list the step kernel wrote).
+// Lanes 0..22 generate the reset event's 23 Philox blocks (tag 1, the env's counter as the step left it) into the warp's scratch,
+// lane 0 then runs the reset against the tile in HBM and writes the observation row - the same tasks in the same arithmetic as the
+// in-kernel reset (reset_env composes them), so the two paths are bit-identical.  The last CTA to finish zeroes the list counters.
+template <bool NOISE>
+__global__ void __launch_bounds__(128) k_reset_list(float* __restrict__ S, int n, const __grid_constant__ DevCfg cfg,
+                                                    const int* __restrict__ list, int* __restrict__ count, float* __restrict__ obs,
+                                                    const float* inj_z, const float* inj_u) {
+    constexpr int OD = NOISE ? 34 : 42;
+    __shared__ float s_draw[4][96];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nd = *reinterpret_cast<volatile const int*>(count);
+    float* zs = s_draw[warp];
+    float* us = zs + CF_RESET_NORMALS;
+    for (int j = blockIdx.x * 4 + warp; j < nd; j += gridDim.x * 4) {
+        const int i = list[j];
+        const EnvRef g = env_ref_global(S, i);
+        const DrawSrc dr = make_draws(cfg, cfg.gid_base + i, g.u(CF_S_RNG_CTR), 1u, inj_z, inj_u, n, i, CF_RESET_UNIFORMS);
+        if (lane < 12) {
+            const float4 v = dr.z(cfg, lane);
+            zs[4 * lane] = v.x; zs[4 * lane + 1] = v.y; zs[4 * lane + 2] = v.z; zs[4 * lane + 3] = v.w;
+        } else if (lane < 23) {
+            const float4 v = dr.u(cfg, lane - 12);
+            us[4 * (lane - 12)] = v.x; us[4 * (lane - 12) + 1] = v.y; us[4 * (lane - 12) + 2] = v.z; us[4 * (lane - 12) + 3] = v.w;
+        }
+        __syncwarp();
+        if (lane == 0) reset_env<NOISE>(g, g, cfg, zs, us, obs + (size_t)i * OD);
+        __syncwarp();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(count + 1, 1) == (int)gridDim.x - 1) { count[0] = 0; count[1] = 0; __threadfence(); }
+    }
 }
 
 // Packed 2-bit sign table of one level from its fp32 value table, with the reference's own
@@ -649,7 +694,7 @@ size_t step_smem_bytes(int obs_dim) {
     return (size_t)(CF_BULK_WORDS + obs_dim + CF_EXTRA_SLOTS) * CF_TILE * 4 + 96 * 4 + 5 * 8 + 8 + CF_TILE + CF_TILE * 4;
 }
 
-template <bool NOISE, int HJ_MODE, bool WS>
+template <bool NOISE, int HJ_MODE, bool WS, bool INRESET>
 static cudaError_t launch_step_variant(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io,
                                        cudaStream_t st) {
     static bool configured[64] = {};                     // per device and variant: opt in to > 48 KB of dynamic shared memory
@@ -657,27 +702,39 @@ static cudaError_t launch_step_variant(float* S, int n, int k, const DevCfg& cfg
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        cudaError_t err = cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t err = cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS, INRESET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
-        cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k_step<NOISE, HJ_MODE, WS, INRESET>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         configured[dev] = true;
     }
-    k_step<NOISE, HJ_MODE, WS><<<blocks_for(n, CF_TILE), WS ? 3 * CF_TILE : CF_TILE, smem, st>>>(S, n, k, cfg, tab, io);
+    k_step<NOISE, HJ_MODE, WS, INRESET><<<blocks_for(n, CF_TILE), WS ? 3 * CF_TILE : CF_TILE, smem, st>>>(S, n, k, cfg, tab, io);
+    if (!INRESET && cfg.auto_reset) {
+        // a warp per finished env (grid-stride): ~1 % of the envs finish per step at the headline workload, up to 2 % with random
+        // actions - one warp per 64 envs keeps it at about one list entry per warp
+        const int grid = (n + 255) / 256;
+        k_reset_list<NOISE><<<grid, 128, 0, st>>>(S, n, cfg, io.reset_list, io.reset_count, io.obs, io.inj_reset_z, io.inj_reset_u);
+    }
     return cudaSuccess;
 }
 cudaError_t launch_step(float* S, int n, int k, const DevCfg& cfg, const DevTables& tab, const StepIO& io, cudaStream_t st) {
     const bool sign = cfg.hj_mode == CF_HJ_SIGN_TABLE;
     static const bool ws = [] { const char* v = getenv("CF_STEP_WS"); return v ? atoi(v) != 0 : (CF_WS_DEFAULT != 0); }();
+    static const bool defer_ok = [] { const char* v = getenv("CF_DEFER_RESET"); return v ? atoi(v) != 0 : true; }();
+    // single-step launches hand finished envs to k_reset_list; K-step launches reset in place (the episode goes on in the launch)
+    const bool inreset = k > 1 || !defer_ok || !io.reset_list;
+#define CF_LAUNCH(NOISE_, WS_)                                                                                                   \
+    do {                                                                                                                         \
+        if (sign) return inreset ? launch_step_variant<NOISE_, CF_HJ_SIGN_TABLE, WS_, true>(S, n, k, cfg, tab, io, st)           \
+                                 : launch_step_variant<NOISE_, CF_HJ_SIGN_TABLE, WS_, false>(S, n, k, cfg, tab, io, st);         \
+        return inreset ? launch_step_variant<NOISE_, CF_HJ_VALUE_TABLE, WS_, true>(S, n, k, cfg, tab, io, st)                    \
+                       : launch_step_variant<NOISE_, CF_HJ_VALUE_TABLE, WS_, false>(S, n, k, cfg, tab, io, st);                  \
+    } while (0)
     if (cfg.obs_noise) {
-        if (ws) {
-            if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE, true>(S, n, k, cfg, tab, io, st);
-            return launch_step_variant<true, CF_HJ_VALUE_TABLE, true>(S, n, k, cfg, tab, io, st);
-        }
-        if (sign) return launch_step_variant<true, CF_HJ_SIGN_TABLE, false>(S, n, k, cfg, tab, io, st);
-        return launch_step_variant<true, CF_HJ_VALUE_TABLE, false>(S, n, k, cfg, tab, io, st);
+        if (ws) CF_LAUNCH(true, true);
+        CF_LAUNCH(true, false);
     }
-    if (sign) return launch_step_variant<false, CF_HJ_SIGN_TABLE, false>(S, n, k, cfg, tab, io, st);
-    return launch_step_variant<false, CF_HJ_VALUE_TABLE, false>(S, n, k, cfg, tab, io, st);
+    CF_LAUNCH(false, false);
+#undef CF_LAUNCH
 }
 void launch_hj_signs(const float* V, uint8_t* P, cudaStream_t st) {
     int nb = (CF_HJ_CELLS + 3) / 4;

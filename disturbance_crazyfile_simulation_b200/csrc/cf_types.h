@@ -91,6 +91,8 @@ struct StepIO {
     const float* pf_act;   // its action rows [pf_n][4] or null
     int pf_tiles, pf_n;
     unsigned long long* trace;   // debug: [n_tiles][CF_TRACE_WORDS] per-CTA timeline (cf_set_trace_buffer) or null
+    int* reset_list;       // deferred resets (single-step launches): env indices that finished an episode in this launch ...
+    int* reset_count;      // ... [0] their number, [1] ticket of the list kernel's CTAs; both zeroed again by k_reset_list
 };
 
 }  // namespace cf
