@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 validation pass on one GPU: all GPU tests, smoke, both bench arms as the driver runs them, other workloads, launch list and
 # full ncu capture of the step kernel and of the policy kernel
-TAG=${1:-r2i}
+TAG=${1:-r2t}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 export CF_HJ_TABLE_CACHE=/tmp/cf_hj_tables
