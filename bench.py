@@ -72,8 +72,9 @@ def parse():
                          "shard's load/store phases overlap another's compute")
     ap.add_argument('--prefetch', action='store_true',
                     help='chain the shards with cf_set_prefetch_next (each step kernel asks the L2 to prefetch the next shard): helped the '
-                         'round-1 kernel at 4 CTAs/SM on two streams, measured -2 % with 5 CTAs/SM on four streams (profiles/r2_kstep_ab.json)')
+                         'round-1 kernel at 4 CTAs/SM on two streams, measured -2 %% with 5 CTAs/SM on four streams (profiles/r2_kstep_ab.json)')
     ap.add_argument('--no-prefetch', action='store_true', help='(default since round 2; kept for old command lines)')
+    ap.add_argument('--fused-update', type=int, default=-1, help='ppo workload: 1 / 0 = policy gradient by the fused kernel / by torch autograd (default: fused)')
     ap.add_argument('--workload', default='hover_hj', choices=['hover_hj', 'initial', 'ppo'],
                     help='hover_hj = BASELINE.json configs[2] (the headline); initial = configs[3] (DroneHoverBulletEnvWithAdversaryInitial-v0, '
                          '131072 envs/GPU); ppo = configs[4] (rollout + fused GAE + PPO update, gradient all-reduce)')
@@ -573,7 +574,7 @@ def main_ppo(args):
         dist.init_process_group('nccl', device_id=dev)
     n, T = args.envs, 32
     env = make(ENV_ID, num_envs=n, seed=2024, env_id_base=rank * n, return_terminal_obs=True, hj_tables='synthetic')
-    tr = PPOTrainer(env, rollout_len=T, epochs=300, seed=1)
+    tr = PPOTrainer(env, rollout_len=T, epochs=300, seed=1, fused_update=None if args.fused_update < 0 else bool(args.fused_update))
     K, W = max(1, min(args.steps, 20)), max(1, min(args.warmup, 3))
     for _ in range(W):
         tr.learn_one_epoch()
@@ -608,6 +609,16 @@ def main_ppo(args):
                'ffma_frac_of_fp32_peak': 2 * macs * n / (us * 1e-6) / peak, 'fp32_peak_tflops_nominal': peak / 1e12}
         upd_floor = (80 * 3 * 2 * (od * 50 + 50 * 50 + 50 * 4) + 5 * 3 * 2 * (od * 64 + 64 * 64 + 64)) * n * T / peak
         pol['update_fp32_ffma_floor_s'] = upd_floor
+        if tr.fused_update:                                  # the fused policy-gradient kernel alone on the last epoch's batch
+            for _ in range(3):
+                tr._fp.pi_grad(tr._g_obs, tr._g_act, tr._g_adv, tr._g_logp, tr.clip_ratio)
+            ev0.record()
+            for _ in range(20):
+                tr._fp.pi_grad(tr._g_obs, tr._g_act, tr._g_adv, tr._g_logp, tr.clip_ratio)
+            ev1.record(); torch.cuda.synchronize()
+            ms = ev0.elapsed_time(ev1) / 20
+            useful = 3 * 2 * (od * 50 + 50 * 50 + 50 * 4) * n * T
+            pol.update(pi_grad_kernel_ms=ms, pi_grad_ffma_frac_of_fp32_peak=useful / (ms * 1e-3) / peak)
     if rank == 0:
         roll = sum(i['rollout_s'] for i in infos) / K
         upd = sum(i['update_s'] for i in infos) / K
@@ -620,7 +631,7 @@ def main_ppo(args):
                                    'gradient all-reduce per optimiser step', 'envs_per_gpu': n, 'rollout_len': T},
             'side': {'rollout_s_per_epoch': roll, 'update_s_per_epoch': upd, 'rollout_env_steps_per_s': n * T * world / roll,
                      'EpRet_last': infos[-1]['EpRet'], 'EpLen_last': infos[-1]['EpLen'], 'reference_logged_fps': '129-172 (BASELINE.md)',
-                     'fused_rollout': bool(tr.fused), 'cuda_graphs': bool(tr.use_graphs), **pol},
+                     'fused_rollout': bool(tr.fused), 'cuda_graphs': bool(tr.use_graphs), 'fused_update': bool(tr.fused_update), **pol},
             'gpu_launches': int(env.launch_count)}), flush=True)
     # captured graphs hold the NCCL all-reduce of the optimiser steps: release them before the communicator goes (destroying
     # the process group under live graphs hung the 2-GPU run of round 2 until its timeout)

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(CSRC, 'libcf_b200.so')
-SOURCES = ['cf_abi.cu', 'cf_kernels.cu', 'cf_policy.cu', 'cf_hj_solver.cu', 'cf_raster.cu']
+SOURCES = ['cf_abi.cu', 'cf_kernels.cu', 'cf_policy.cu', 'cf_ppo.cu', 'cf_hj_solver.cu', 'cf_raster.cu']
 DEPS = SOURCES + ['cf_device.cuh', 'cf_types.h', 'cf_kernels.h', os.path.join('..', '..', 'include', 'cf_abi.h')]
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-shared', '-cudart', 'static']

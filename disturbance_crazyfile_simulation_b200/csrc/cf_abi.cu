@@ -773,6 +773,51 @@ int cf_policy_step_dev(cf_env* e, const cf_policy_weights* w, const float* obs, 
     return CF_OK;
 }
 
+static const int kPpoCtas = 296;                             // persistent CTAs of the fused update kernel (2 per SM on 148 SMs)
+int cf_ppo_workspace_floats(void) { return kPpoCtas * ppo_partial_floats(); }
+
+int cf_ppo_pi_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* act, const float* adv,
+                       const float* logp_old, int64_t B, float clip_ratio, float* const grad_w[3], float* const grad_b[3],
+                       float* loss_ratio, float* workspace, void* stream) {
+    if (!w || !obs || !act || !adv || !logp_old || !grad_w || !grad_b || !loss_ratio || !workspace || B < 1 || B > 0x7fffffff)
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad: bad argument%s", "");
+    if ((obs_dim != 34 && obs_dim != 42) || w->pi_hidden < 1 || w->pi_hidden > 64 || !w->log_std)
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad: obs_dim must be 34 or 42, hidden width 1..64%s", "");
+    if (((uintptr_t)obs & 7) || ((uintptr_t)act & 15)) return fail(CF_ERR_INVALID, "cf_ppo_pi_grad: obs must be 8-byte, act 16-byte aligned%s", "");
+    PpoHostArgs a{};
+    a.net = 0; a.obs = obs; a.act = act; a.adv = adv; a.logp_old = logp_old; a.log_std = w->log_std;
+    for (int l = 0; l < 3; ++l) {
+        if (!w->pi_w[l] || !w->pi_b[l] || !grad_w[l] || !grad_b[l]) return fail(CF_ERR_INVALID, "cf_ppo_pi_grad: null tensor%s", "");
+        a.w[l] = w->pi_w[l]; a.b[l] = w->pi_b[l]; a.gw[l] = grad_w[l]; a.gb[l] = grad_b[l];
+    }
+    a.loss_ratio = loss_ratio; a.partial = workspace; a.B = (int)B; a.obs_dim = obs_dim; a.h = w->pi_hidden; a.n_cta = kPpoCtas;
+    a.clip = clip_ratio;
+    cudaError_t err = launch_ppo_grad(a, (cudaStream_t)stream);
+    if (err != cudaSuccess) return cuda_fail(err, "launch_ppo_grad");
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
+int cf_ppo_v_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* target_v, const int64_t* idx,
+                      int64_t B, float* const grad_w[3], float* const grad_b[3], float* loss, float* workspace, void* stream) {
+    if (!w || !obs || !target_v || !grad_w || !grad_b || !loss || !workspace || B < 1 || B > 0x7fffffff)
+        return fail(CF_ERR_INVALID, "cf_ppo_v_grad: bad argument%s", "");
+    if ((obs_dim != 34 && obs_dim != 42) || w->v_hidden < 1 || w->v_hidden > 64)
+        return fail(CF_ERR_INVALID, "cf_ppo_v_grad: obs_dim must be 34 or 42, hidden width 1..64%s", "");
+    if ((uintptr_t)obs & 7) return fail(CF_ERR_INVALID, "cf_ppo_v_grad: obs must be 8-byte aligned%s", "");
+    PpoHostArgs a{};
+    a.net = 1; a.obs = obs; a.tgt = target_v; a.idx = (const long long*)idx;
+    for (int l = 0; l < 3; ++l) {
+        if (!w->v_w[l] || !w->v_b[l] || !grad_w[l] || !grad_b[l]) return fail(CF_ERR_INVALID, "cf_ppo_v_grad: null tensor%s", "");
+        a.w[l] = w->v_w[l]; a.b[l] = w->v_b[l]; a.gw[l] = grad_w[l]; a.gb[l] = grad_b[l];
+    }
+    a.loss_ratio = loss; a.partial = workspace; a.B = (int)B; a.obs_dim = obs_dim; a.h = w->v_hidden; a.n_cta = kPpoCtas;
+    cudaError_t err = launch_ppo_grad(a, (cudaStream_t)stream);
+    if (err != cudaSuccess) return cuda_fail(err, "launch_ppo_grad");
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
 int cf_pd_actions_dev(const float* obs, int32_t obs_dim, int32_t n, float* act, const float gains[6], void* stream) {
     if (!obs || !act || !gains || n < 1 || (obs_dim != 34 && obs_dim != 42) || ((uintptr_t)act & 15))
         return fail(CF_ERR_INVALID, "cf_pd_actions: bad argument%s", "");

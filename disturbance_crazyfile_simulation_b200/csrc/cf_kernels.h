@@ -36,6 +36,20 @@ struct PolicyHostArgs {
     float eps;
 };
 cudaError_t launch_policy(const PolicyHostArgs& h, const DevCfg& cfg, cudaStream_t st);
+// fused PPO policy update step (cf_ppo.cu): forward + clipped-surrogate loss + backward for pi.net; device pointers
+struct PpoHostArgs {
+    const float *obs, *act, *adv, *logp_old;      // [B][obs_dim] standardised, [B][4], [B], [B]   (policy net)
+    const float* tgt; const long long* idx;       // value net: targets [all], mini-batch sample indices [B] (or null)
+    int net;                                      // 0 policy (pi.net), 1 value (v.net)
+    const float *w[3], *b[3], *log_std;           // net.{0,2,4} in torch layout, pi.log_std
+    float *gw[3], *gb[3];                         // gradient tensors, same layouts
+    float* loss_ratio;                            // [2]: mean loss, mean ratio (policy)
+    float* partial;                               // workspace [n_cta][ppo_partial_floats()]
+    int B, obs_dim, h, n_cta;
+    float clip;
+};
+cudaError_t launch_ppo_grad(const PpoHostArgs& a, cudaStream_t st);
+int ppo_partial_floats();
 void set_error(const char* where, const char* what);     // cf_abi.cu: text behind cf_last_error()
 struct PdGains { float hover, kz, kvz, katt, krate, kyaw; };
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st);

@@ -73,3 +73,64 @@ class FusedPolicy:
                                              C.c_void_p(act.data_ptr()), C.c_void_p(val.data_ptr()), C.c_void_p(logp.data_ptr()),
                                              stream))
         return act, val, logp
+
+    # ------------------------------------------------------------------ fused policy-update step (cf_ppo_pi_grad_dev)
+    def pi_grad(self, obs_norm: torch.Tensor, act: torch.Tensor, adv: torch.Tensor, logp_old: torch.Tensor, clip_ratio: float):
+        """One iteration of ``update_policy_net`` up to the optimiser step (iwpg.py:448-459; ``compute_loss_pi`` of
+        ppo.py:22-40 + ``backward``) in one kernel: fills ``.grad`` of the six ``pi.net`` tensors and returns
+        (mean surrogate loss, mean ratio) as 0-d device tensors.  ``obs_norm`` are the STANDARDISED observations."""
+        dev = self.env.device
+        B = obs_norm.shape[0]
+        for t, shape in ((obs_norm, (B, self.env.obs_dim)), (act, (B, 4)), (adv, (B,)), (logp_old, (B,))):
+            if t.shape != shape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+                raise ValueError(f'pi_grad: expected contiguous float32 {shape} on {dev}')
+        lins = _linears(self.ac.pi.net)
+        if getattr(self, '_ppo_ws', None) is None:
+            self._ppo_ws = torch.empty(self._L.cf_ppo_workspace_floats(), dtype=torch.float32, device=dev)
+            self._ppo_lr = torch.zeros(2, dtype=torch.float32, device=dev)
+        for l in lins:
+            for p in (l.weight, l.bias):
+                if p.grad is None:
+                    p.grad = torch.zeros_like(p)
+        gw = (C.c_void_p * 3)(*[l.weight.grad.data_ptr() for l in lins])
+        gb = (C.c_void_p * 3)(*[l.bias.grad.data_ptr() for l in lins])
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        abi.check(self._L.cf_ppo_pi_grad_dev(C.byref(self._w), self.env.obs_dim, C.c_void_p(obs_norm.data_ptr()),
+                                             C.c_void_p(act.data_ptr()), C.c_void_p(adv.data_ptr()), C.c_void_p(logp_old.data_ptr()),
+                                             B, float(clip_ratio), gw, gb, C.c_void_p(self._ppo_lr.data_ptr()),
+                                             C.c_void_p(self._ppo_ws.data_ptr()), stream))
+        return self._ppo_lr[0], self._ppo_lr[1]
+
+    def v_grad(self, obs_norm: torch.Tensor, target_v: torch.Tensor, perm: Optional[torch.Tensor], start: int, count: int):
+        """One mini-batch iteration of ``update_value_net`` up to the optimiser step (iwpg.py:478-510): fills ``.grad`` of the six
+        ``v.net`` tensors for rows ``perm[start:start + count]`` of the epoch's batch (``perm`` None: rows start..start+count-1 need
+        start == 0) and returns the mean squared error as a 0-d device tensor."""
+        dev = self.env.device
+        n = obs_norm.shape[0]
+        if obs_norm.shape != (n, self.env.obs_dim) or obs_norm.dtype != torch.float32 or not obs_norm.is_contiguous() or obs_norm.device != dev:
+            raise ValueError('v_grad: obs must be contiguous float32 [n, obs_dim] on the env device')
+        if target_v.shape != (n,) or target_v.dtype != torch.float32 or not target_v.is_contiguous():
+            raise ValueError('v_grad: target_v must be contiguous float32 [n]')
+        if perm is None:
+            if start != 0 or not 0 < count <= n:
+                raise ValueError('v_grad without perm covers rows 0..count-1')
+            idx = None
+        else:
+            if perm.dtype != torch.int64 or perm.dim() != 1 or not perm.is_contiguous() or start < 0 or count < 1 or start + count > perm.numel():
+                raise ValueError('v_grad: perm must be a contiguous int64 vector covering start..start+count')
+            idx = perm.data_ptr() + 8 * start
+        lins = _linears(self.ac.v.net)
+        if getattr(self, '_ppo_ws_v', None) is None:
+            self._ppo_ws_v = torch.empty(self._L.cf_ppo_workspace_floats(), dtype=torch.float32, device=dev)
+            self._ppo_lv = torch.zeros(2, dtype=torch.float32, device=dev)
+        for l in lins:
+            for p in (l.weight, l.bias):
+                if p.grad is None:
+                    p.grad = torch.zeros_like(p)
+        gw = (C.c_void_p * 3)(*[l.weight.grad.data_ptr() for l in lins])
+        gb = (C.c_void_p * 3)(*[l.bias.grad.data_ptr() for l in lins])
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        abi.check(self._L.cf_ppo_v_grad_dev(C.byref(self._w), self.env.obs_dim, C.c_void_p(obs_norm.data_ptr()),
+                                            C.c_void_p(target_v.data_ptr()), C.c_void_p(idx), count, gw, gb,
+                                            C.c_void_p(self._ppo_lv.data_ptr()), C.c_void_p(self._ppo_ws_v.data_ptr()), stream))
+        return self._ppo_lv[0]

@@ -139,7 +139,8 @@ class PPOTrainer:
                  use_exploration_noise_anneal: bool = True, use_kl_early_stopping: bool = False,
                  target_kl: float = 0.01, check_freq: int = 25, seed: int = 0, actor_critic: Optional[ActorCritic] = None,
                  gae_fn=None, logger=None, save_freq: int = 10, val_freq: int = 0, val_kwargs: Optional[dict] = None,
-                 fused_rollout: Optional[bool] = None, use_cuda_graphs: Optional[bool] = None, episode_rows_per_epoch: int = 256):
+                 fused_rollout: Optional[bool] = None, use_cuda_graphs: Optional[bool] = None, episode_rows_per_epoch: int = 256,
+                 fused_update: Optional[bool] = None):
         # fused_rollout (default: on for a CUDA CrazyFlieVecEnv): the two networks of ac.step run as ONE kernel per control step
         # (policy.FusedPolicy / cf_policy_step_dev) that writes straight into the rollout buffers, the env writes its rows
         # straight into them too (no copies), and the T x 2 launches of a rollout are replayed from one CUDA graph;
@@ -180,6 +181,12 @@ class PPOTrainer:
         self.use_graphs = (self.dev.type == 'cuda') if use_cuda_graphs is None else bool(use_cuda_graphs)
         if self.fused and not on_gpu_env:
             raise ValueError('fused_rollout needs a CUDA CrazyFlieVecEnv')
+        # fused_update (default: with the fused rollout and CUDA graphs): every optimiser step of either network runs forward + loss +
+        # backward as one kernel (cf_ppo_pi_grad_dev / cf_ppo_v_grad_dev) instead of ~40 torch kernels; the gradient all-reduce
+        # and Adam stay in torch
+        self.fused_update = (self.fused and self.use_graphs) if fused_update is None else bool(fused_update)
+        if self.fused_update and not (self.fused and self.use_graphs):
+            raise ValueError('fused_update needs fused_rollout and use_cuda_graphs')
         self._obs_all = torch.empty((T + 1, N, od), **f)     # row t: observation the policy sees at step t; row T: after the last step
         self.obs_buf = self._obs_all[:T]
         self.act_buf = torch.empty((T, N, 4), **f)
@@ -397,6 +404,11 @@ class PPOTrainer:
 
     def _v_minibatches(self, mbs: int) -> None:
         for start in range(0, mbs * self.num_mini_batches, mbs):
+            if self.fused_update:                            # forward + loss + backward of v.net in one kernel (cf_ppo_v_grad_dev)
+                self._fp.v_grad(self._g_obs, self._g_tgt, self._g_perm, start, mbs)
+                self._avg_v()
+                self.vf_optimizer.step()
+                continue
             idx = self._g_perm[start:start + mbs]
             self.vf_optimizer.zero_grad(set_to_none=False)
             loss_v = ((self.ac.v(self._g_obs[idx]) - self._g_tgt[idx]) ** 2).mean()
@@ -405,6 +417,12 @@ class PPOTrainer:
             self.vf_optimizer.step()
 
     def _pi_step(self):
+        if self.fused_update:
+            # forward + clipped surrogate + backward of pi.net in one kernel (cf_ppo_pi_grad_dev): .grad is written directly
+            loss, ratio = self._fp.pi_grad(self._g_obs, self._g_act, self._g_adv, self._g_logp, self.clip_ratio)
+            self._avg_pi()
+            self.pi_optimizer.step()
+            return loss - self.entropy_coef * self.ac.pi.entropy().detach(), ratio
         self.pi_optimizer.zero_grad(set_to_none=False)
         loss_pi, _, ratio = self.compute_loss_pi(self._g_obs, self._g_act, self._g_adv, self._g_logp)
         loss_pi.backward()

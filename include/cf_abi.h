@@ -258,6 +258,25 @@ typedef struct cf_policy_weights {
 int cf_policy_step_dev(cf_env* env, const cf_policy_weights* w, const float* obs, int32_t deterministic, float* act, float* val,
                        float* logp, void* stream);
 
+/* One policy-update iteration of PPO up to the optimiser step, fused (IWPGAlgorithm.update_policy_net, algs/iwpg/iwpg.py:448-459:
+ * compute_loss_pi of algs/ppo/ppo.py:22-40 + loss.backward()): forward of the policy MLP on the standardised observations,
+ * Gaussian log-prob of the stored actions, ratio, clipped surrogate -mean(min(ratio adv, clip(ratio, 1 - c, 1 + c) adv)) and the
+ * gradients of the six pi.net tensors, in ONE kernel over tiles of 128 samples + a deterministic reduction.  All DEVICE pointers;
+ * weights and gradients in torch's nn.Linear layout [out][in] (w->pi_w / pi_b / log_std / pi_hidden are read, the rest of the
+ * struct is ignored); obs [B][obs_dim] ALREADY standardised (pre_process_data, iwpg.py:350-370), act [B][4] 16-byte aligned,
+ * adv [B], logp_old [B]; grad_w[l] / grad_b[l] receive d loss / d pi.net.{0,2,4}.{weight,bias}; loss_ratio [2] = mean loss (without
+ * the entropy bonus, which has no gradient: log_std is not trained), mean ratio; workspace: cf_ppo_workspace_floats() floats. */
+int cf_ppo_workspace_floats(void);
+int cf_ppo_pi_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* act, const float* adv,
+                       const float* logp_old, int64_t B, float clip_ratio, float* const grad_w[3], float* const grad_b[3],
+                       float* loss_ratio, float* workspace, void* stream);
+/* One mini-batch step of the value update up to the optimiser step, the same way (IWPGAlgorithm.update_value_net,
+ * algs/iwpg/iwpg.py:478-510; loss = mean((v(obs[idx]) - target_v[idx])^2), iwpg.py:250-255): v.net forward (tanh), loss and the six
+ * gradients.  obs [all][obs_dim] standardised, target_v [all]; idx [B] int64 rows of this mini-batch (torch.randperm slice), or
+ * NULL for rows 0..B-1; w->v_w / v_b / v_hidden are read; loss [2]: loss[0] = mean squared error (loss[1] unused). */
+int cf_ppo_v_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* target_v, const int64_t* idx,
+                      int64_t B, float* const grad_w[3], float* const grad_b[3], float* loss, float* workspace, void* stream);
+
 /* ---- synthetic "PID actions" source of the throughput runs ------------------------------------
  * Attitude -> rate -> motor-mix PD law on the NOISY observation rows (device pointers, asynchronous): structure of
  * the firmware cascade the reference cites (envs/control.py:13-26 gains, :33-50 rpy_control_factors_to_PWM,
