@@ -113,6 +113,8 @@ _SIGS = {
     'cf_ppo_workspace_floats': (C.c_int, []),
     'cf_ppo_pi_grad_dev': (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, C.c_int64, C.c_float, _P, _P, _P, _P, _P]),
     'cf_ppo_v_grad_dev': (C.c_int, [_P, C.c_int32, _P, _P, _P, C.c_int64, _P, _P, _P, _P, _P]),
+    'cf_ppo_static_max_samples': (C.c_int64, []),
+    'cf_ppo_pi_grad_static_dev': (C.c_int, [_P, C.c_int32, _P, _P, _P, _P, C.c_int64, C.c_float, _P, _P, _P, _P]),
     'cf_pd_actions_dev': (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P]),
     'cf_raster_create': (C.c_int, [_P, C.c_int32, _P, _P, C.c_int32, C.c_float]),
     'cf_raster_destroy': (None, [_P]),

@@ -798,6 +798,36 @@ int cf_ppo_pi_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float*
     return CF_OK;
 }
 
+// The allocation-free variant of cf_ppo_pi_grad_dev: no workspace argument, the per-CTA partial sums go to a file-scope
+// __device__ array of cf_ppo.cu (address resolved there with cudaGetSymbolAddress, once per device).  Calls nothing that
+// allocates: no cudaMalloc / cudaFree, no library routine; the error text goes to a thread-local buffer.
+int64_t cf_ppo_static_max_samples(void) { return (int64_t)ppo_static_max_samples(); }
+
+int cf_ppo_pi_grad_static_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* act, const float* adv,
+                              const float* logp_old, int64_t B, float clip_ratio, float* const grad_w[3], float* const grad_b[3],
+                              float* loss_ratio, void* stream) {
+    if (!w || !obs || !act || !adv || !logp_old || !grad_w || !grad_b || !loss_ratio || B < 1)
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad_static: bad argument%s", "");
+    if (B > ppo_static_max_samples())
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad_static: %s%lld samples exceed the static scratch's limit of 4194304 "
+                                    "(cf_ppo_static_max_samples); use cf_ppo_pi_grad_dev with a caller workspace", "", (long long)B);
+    if ((obs_dim != 34 && obs_dim != 42) || w->pi_hidden < 1 || w->pi_hidden > 64 || !w->log_std)
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad_static: obs_dim must be 34 or 42, hidden width 1..64%s", "");
+    if (((uintptr_t)obs & 7) || ((uintptr_t)act & 15))
+        return fail(CF_ERR_INVALID, "cf_ppo_pi_grad_static: obs must be 8-byte, act 16-byte aligned%s", "");
+    PpoHostArgs a{};
+    a.net = 0; a.obs = obs; a.act = act; a.adv = adv; a.logp_old = logp_old; a.log_std = w->log_std;
+    for (int l = 0; l < 3; ++l) {
+        if (!w->pi_w[l] || !w->pi_b[l] || !grad_w[l] || !grad_b[l]) return fail(CF_ERR_INVALID, "cf_ppo_pi_grad_static: null tensor%s", "");
+        a.w[l] = w->pi_w[l]; a.b[l] = w->pi_b[l]; a.gw[l] = grad_w[l]; a.gb[l] = grad_b[l];
+    }
+    a.loss_ratio = loss_ratio; a.B = (int)B; a.obs_dim = obs_dim; a.h = w->pi_hidden; a.clip = clip_ratio;
+    cudaError_t err = launch_ppo_pi_grad_static(a, (cudaStream_t)stream);
+    if (err != cudaSuccess) return cuda_fail(err, "launch_ppo_pi_grad_static (cudaGetSymbolAddress / launch)");
+    CU(cudaGetLastError());
+    return CF_OK;
+}
+
 int cf_ppo_v_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* target_v, const int64_t* idx,
                       int64_t B, float* const grad_w[3], float* const grad_b[3], float* loss, float* workspace, void* stream) {
     if (!w || !obs || !target_v || !grad_w || !grad_b || !loss || !workspace || B < 1 || B > 0x7fffffff)

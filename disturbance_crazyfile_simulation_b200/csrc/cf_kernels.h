@@ -50,6 +50,9 @@ struct PpoHostArgs {
 };
 cudaError_t launch_ppo_grad(const PpoHostArgs& a, cudaStream_t st);
 int ppo_partial_floats();
+cudaError_t launch_ppo_pi_grad_static(const PpoHostArgs& a, cudaStream_t st);    // scratch in a file-scope __device__ array of cf_ppo.cu
+int ppo_static_max_ctas();
+long long ppo_static_max_samples();
 void set_error(const char* where, const char* what);     // cf_abi.cu: text behind cf_last_error()
 struct PdGains { float hover, kz, kvz, katt, krate, kyaw; };
 void launch_pd_actions(const float* obs, int obs_dim, int off, int n, float* act, const PdGains& g, cudaStream_t st);

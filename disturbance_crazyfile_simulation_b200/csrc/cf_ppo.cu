@@ -357,4 +357,38 @@ cudaError_t launch_ppo_grad(const PpoHostArgs& a, cudaStream_t st) {
     return cudaSuccess;
 }
 
+// ---- the allocation-free variant (cf_ppo_pi_grad_static_dev) ----------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The per-CTA partial-sum records live in this
+// file-scope array instead of a caller workspace: kStaticCtas x kPartial floats = 148 x 7560 x 4 B = 4.27 MiB, held by every
+// GPU that loads the library until the process exits.  Every launch overwrites each record its reduction later reads (all
+// kPartial words of records 0 .. grid - 1), so nothing has to start at zero and a call does not see the previous call's
+// contents; all calls share the one array, so calls that overlap on the GPU (different streams, other threads) race.
+constexpr int kStaticCtas = 148;                          // one persistent CTA per SM
+constexpr long long kStaticMaxB = 1ll << 22;              // 4 194 304 samples: 222 tiles per CTA, twice the PPO bench's batch
+static __device__ __align__(256) float g_ppo_static_scratch[kStaticCtas * kPartial];
+
+int ppo_static_max_ctas() { return kStaticCtas; }
+long long ppo_static_max_samples() { return kStaticMaxB; }
+
+// In host code g_ppo_static_scratch is a stand-in for the symbol, not a device address: the address is resolved once per
+// device, with that device current, and cached.  a.partial and a.n_cta are ignored.
+cudaError_t launch_ppo_pi_grad_static(const PpoHostArgs& a, cudaStream_t st) {
+    static float* scratch[64] = {};
+    int dev = -1;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err != cudaSuccess) return err;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!scratch[dev]) {
+        float* ptr = nullptr;
+        err = cudaGetSymbolAddress((void**)&ptr, g_ppo_static_scratch);
+        if (err != cudaSuccess) return err;
+        if (!ptr) return cudaErrorInvalidSymbol;
+        scratch[dev] = ptr;
+    }
+    PpoHostArgs b = a;
+    b.net = 0; b.partial = scratch[dev]; b.n_cta = kStaticCtas;
+    return launch_ppo_grad(b, st);
+}
+
 }  // namespace cf

@@ -270,6 +270,22 @@ int cf_ppo_workspace_floats(void);
 int cf_ppo_pi_grad_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* act, const float* adv,
                        const float* logp_old, int64_t B, float clip_ratio, float* const grad_w[3], float* const grad_b[3],
                        float* loss_ratio, float* workspace, void* stream);
+/* cf_ppo_pi_grad_dev without a workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and arithmetic as cf_ppo_pi_grad_dev; the per-CTA partial sums (the kernel's scratch)
+ * live in a file-scope `static __device__ __align__(256)` array of 148 x 7560 floats = 4.27 MiB, which every GPU that loads the
+ * library holds until the process exits.  LIMIT: B <= cf_ppo_static_max_samples() = 4 194 304 samples; more is rejected with
+ * CF_ERR_INVALID and a message naming the limit.  The call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine; on the first call per device it resolves the array's address (cudaGetSymbolAddress).  It runs 148 persistent CTAs
+ * where cf_ppo_pi_grad_dev runs 296, so the two sum in a different order: results agree to float32 rounding (2e-5 of each
+ * tensor's largest entry in tests/test_zz_no_alloc.py), not bit for bit.  ALL CALLS SHARE THE ONE ARRAY: it keeps the last
+ * call's contents (every launch overwrites all it reads, nothing needs clearing), and calls that overlap on the GPU - other
+ * streams, other host threads - race on it; order them on one stream or with events. */
+int64_t cf_ppo_static_max_samples(void);
+int cf_ppo_pi_grad_static_dev(const cf_policy_weights* w, int32_t obs_dim, const float* obs, const float* act, const float* adv,
+                              const float* logp_old, int64_t B, float clip_ratio, float* const grad_w[3], float* const grad_b[3],
+                              float* loss_ratio, void* stream);
+
 /* One mini-batch step of the value update up to the optimiser step, the same way (IWPGAlgorithm.update_value_net,
  * algs/iwpg/iwpg.py:478-510; loss = mean((v(obs[idx]) - target_v[idx])^2), iwpg.py:250-255): v.net forward (tanh), loss and the six
  * gradients.  obs [all][obs_dim] standardised, target_v [all]; idx [B] int64 rows of this mini-batch (torch.randperm slice), or
