@@ -619,6 +619,16 @@ def main_ppo(args):
             ms = ev0.elapsed_time(ev1) / 20
             useful = 3 * 2 * (od * 50 + 50 * 50 + 50 * 4) * n * T
             pol.update(pi_grad_kernel_ms=ms, pi_grad_ffma_frac_of_fp32_peak=useful / (ms * 1e-3) / peak)
+    # the ranks apply the same all-reduced gradients from the same initial weights: their parameters must stay identical
+    rank_diff = 0.0
+    if world > 1:
+        flat = torch.cat([p.detach().reshape(-1) for p in tr.ac.parameters()])
+        ref = flat.clone()
+        dist.broadcast(ref, src=0)
+        dmax = (flat - ref).abs().max().reshape(1)
+        dist.all_reduce(dmax, op=dist.ReduceOp.MAX)
+        rank_diff = float(dmax.item())
+        pol['param_max_diff_across_ranks'] = rank_diff
     if rank == 0:
         roll = sum(i['rollout_s'] for i in infos) / K
         upd = sum(i['update_s'] for i in infos) / K
