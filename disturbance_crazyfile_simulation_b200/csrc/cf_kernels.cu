@@ -554,6 +554,12 @@ __global__ void k_gae(const float* __restrict__ rew, const float* __restrict__ v
 #ifndef CF_GAE_U
 #define CF_GAE_U 2
 #endif
+// (U, min CTAs/SM, threads) sweep on one box, T = 32 x N = 524 288, 20 launches (tools/gpu_r2_gae_sweep.sh): (2,7,128) 62.9 us =
+// 5.60 TB/s = 0.856 of the measured HBM peak; (1,8,128) 62.9; (2,14,64) 62.6; (2,8,128) 65.7; (2,4,256) 67.1; U = 3 / 4 spill: 80-83 us.
+// At N = 2 097 152 the same kernel reaches 5.94 TB/s = 0.91: what is missing at the bench size is the ramp and tail of a 63 us kernel.
+#ifndef CF_GAE_THREADS
+#define CF_GAE_THREADS 128
+#endif
 #ifndef CF_GAE_MIN_CTAS
 #define CF_GAE_MIN_CTAS 7                /* <= 72 registers: N = 524 288 columns (1 024 CTAs) are one wave on 148 SMs */
 #endif
@@ -573,7 +579,7 @@ __device__ __forceinline__ void gae_lane(GaeLane& s, float r, float v, bool d, f
     ret = (float)s.run_ret;
     s.next_val = (double)v;
 }
-__global__ void __launch_bounds__(128, CF_GAE_MIN_CTAS) k_gae4(const float4* __restrict__ rew, const float4* __restrict__ val,
+__global__ void __launch_bounds__(CF_GAE_THREADS, CF_GAE_MIN_CTAS) k_gae4(const float4* __restrict__ rew, const float4* __restrict__ val,
                                               const uchar4* __restrict__ done, const float4* __restrict__ end_val,
                                               const float4* __restrict__ last_val, float gamma, float lam, float rew_scale, int T,
                                               int N4, float4* __restrict__ adv, float4* __restrict__ tgt, float4* __restrict__ disc_ret) {
@@ -778,7 +784,7 @@ void launch_gae(const float* rew, const float* val, const uint8_t* done, const f
     const uintptr_t al = (uintptr_t)rew | (uintptr_t)val | (uintptr_t)end_val | (uintptr_t)last_val | (uintptr_t)adv | (uintptr_t)tgt |
                          (uintptr_t)disc_ret;
     if (N % 4 == 0 && (al & 15) == 0 && ((uintptr_t)done & 3) == 0) {
-        k_gae4<<<blocks_for(N / 4, 128), 128, 0, st>>>(
+        k_gae4<<<blocks_for(N / 4, CF_GAE_THREADS), CF_GAE_THREADS, 0, st>>>(
             reinterpret_cast<const float4*>(rew), reinterpret_cast<const float4*>(val), reinterpret_cast<const uchar4*>(done),
             reinterpret_cast<const float4*>(end_val), reinterpret_cast<const float4*>(last_val), gamma, lam, rew_scale, T, N / 4,
             reinterpret_cast<float4*>(adv), reinterpret_cast<float4*>(tgt), reinterpret_cast<float4*>(disc_ret));
