@@ -64,6 +64,7 @@ def parse():
     ap.add_argument('--shards', type=int, default=16, help='independent env shards per GPU (L2 eviction; every shard is its own handle)')
     ap.add_argument('--kfuse', type=int, default=32, help='control steps per launch in the fused side measurement')
     ap.add_argument('--e2e-steps', type=int, default=200)
+    ap.add_argument('--e2e-depth', type=int, default=8, help='host-pointer steps in flight (pinned buffer sets; at most one per shard) of the e2e measurement')
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--graph-passes', type=int, default=4, help='round-robin passes over the shards captured in the CUDA graph')
@@ -465,7 +466,7 @@ def main_ours(args):
         return np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(ptr)).view(dtype).reshape(shape), ptr
     # D buffer sets in flight: shard i's download overlaps shard i+1's upload and kernel (cf_step_host_async + cf_host_sync);
     # every step still uploads its actions from pinned host memory and downloads obs / rew / done / cost into it
-    D = min(3, S)
+    D = max(1, min(args.e2e_depth, S))
     sets, ptrs = [], []
     for _ in range(D):
         bufs = [pinned((n, 4), np.float32), pinned((n, od), np.float32), pinned((n,), np.float32), pinned((n,), np.uint8),

@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <time.h>
 
 #include <new>
 #include <vector>
@@ -65,6 +66,8 @@ struct cf_env {
     float* rec_dev = nullptr;        // scratch for get/set_state
     // host-pointer API: private stream + device mirrors of the caller's host buffers
     cudaStream_t hstream = nullptr;
+    cudaEvent_t probe_ev[5] = {};                           // tools/ only: CF_PROBE_E2E_TIMELINE (see step_host_enqueue)
+    double probe_cpu[3] = {};                               // CPU clock [ms]: enqueue entry, enqueue return, sync entry
     // ordering between the two call families on one handle (both touch S): 1 = device-pointer API on the caller's stream,
     // 2 = host-pointer API on hstream; on a switch the new stream waits for an event recorded on the previous one
     cudaEvent_t order_ev = nullptr;
@@ -514,6 +517,27 @@ int cf_reset_host(cf_env* e, const uint8_t* mask, float* obs) {
     return CF_OK;
 }
 
+// tools/ only: CF_PROBE_E2E_TIMELINE=<csv path> records CUDA events around the upload, the kernels, the observation download and
+// the last small download of every host-pointer step against one process-wide origin and writes them at exit (no nsys here).
+struct HostTimeline {
+    const char* path = getenv("CF_PROBE_E2E_TIMELINE");
+    cudaEvent_t origin = nullptr;
+    std::vector<float> rows;                                   // 10 floats per step: handle tag, t0..t4 [ms since origin], 4 CPU times
+    double cpu0 = 0.0;
+    static double now_ms() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return 1e3 * ts.tv_sec + 1e-6 * ts.tv_nsec; }
+    ~HostTimeline() {
+        if (!path || rows.empty()) return;
+        if (FILE* f = fopen(path, "w")) {
+            fprintf(f, "handle,before_h2d,after_h2d,after_kernels,after_obs_d2h,after_small_d2h,cpu_enq_in,cpu_enq_out,cpu_sync_in,cpu_sync_out\n");
+            for (size_t k = 0; k + 10 <= rows.size(); k += 10)
+                fprintf(f, "%d,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f,%.4f\n", (int)rows[k], rows[k + 1], rows[k + 2], rows[k + 3], rows[k + 4],
+                        rows[k + 5], rows[k + 6], rows[k + 7], rows[k + 8], rows[k + 9]);
+            fclose(f);
+        }
+    }
+};
+static HostTimeline g_timeline;
+
 static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew, uint8_t* done, float* cost, float* term_obs,
                              uint8_t* truncated, bool wait) {
     if (!e || !act || !obs || !rew || !done) return fail(CF_ERR_INVALID, "cf_step: null argument%s", "");
@@ -528,18 +552,30 @@ static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew
     if (rc == CF_OK && truncated) rc = ensure(&e->d_trunc, n);
     if (rc != CF_OK) return rc;
     cudaStream_t st = e->hstream;
-    // pinned caller buffers make these true async DMA transfers; pageable ones are staged by the driver
+    const bool tl = g_timeline.path != nullptr;
+    if (tl) {
+        if (!g_timeline.origin) { CU(cudaEventCreate(&g_timeline.origin)); CU(cudaEventRecord(g_timeline.origin, st)); g_timeline.cpu0 = HostTimeline::now_ms(); }
+        e->probe_cpu[0] = HostTimeline::now_ms() - g_timeline.cpu0;
+        for (int k = 0; k < 5; ++k) if (!e->probe_ev[k]) CU(cudaEventCreate(&e->probe_ev[k]));
+        CU(cudaEventRecord(e->probe_ev[0], st));
+    }
+    // pinned caller buffers make these true async DMA transfers; pageable ones are staged by the driver.  (An upload by kernel
+    // from the pinned buffer was measured against this copy and is never faster: profiles/r2_e2e_timeline.md.)
     CU(cudaMemcpyAsync(e->d_act, act, n * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (tl) CU(cudaEventRecord(e->probe_ev[1], st));
     if (term_obs) CU(cudaMemcpyAsync(e->d_term, term_obs, n * od * sizeof(float), cudaMemcpyHostToDevice, st));
     rc = step_common(e, 1, e->d_act, e->d_obs, e->d_rew, e->d_done, cost ? e->d_cost : nullptr,
                      term_obs ? e->d_term : nullptr, truncated ? e->d_trunc : nullptr, st);
     if (rc != CF_OK) return rc;
+    if (tl) CU(cudaEventRecord(e->probe_ev[2], st));
     CU(cudaMemcpyAsync(obs, e->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (tl) CU(cudaEventRecord(e->probe_ev[3], st));
     CU(cudaMemcpyAsync(rew, e->d_rew, n * sizeof(float), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(done, e->d_done, n, cudaMemcpyDeviceToHost, st));
     if (cost) CU(cudaMemcpyAsync(cost, e->d_cost, n * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (term_obs) CU(cudaMemcpyAsync(term_obs, e->d_term, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (truncated) CU(cudaMemcpyAsync(truncated, e->d_trunc, n, cudaMemcpyDeviceToHost, st));
+    if (tl) { CU(cudaEventRecord(e->probe_ev[4], st)); e->probe_cpu[1] = HostTimeline::now_ms() - g_timeline.cpu0; }
     if (wait) CU(cudaStreamSynchronize(st));
     return CF_OK;
 }
@@ -555,7 +591,17 @@ int cf_step_host_async(cf_env* e, const float* act, float* obs, float* rew, uint
 int cf_host_sync(cf_env* e) {
     if (!e) return fail(CF_ERR_INVALID, "cf_host_sync: null handle%s", "");
     CU(cudaSetDevice(e->device));
+    if (g_timeline.path) e->probe_cpu[2] = HostTimeline::now_ms() - g_timeline.cpu0;
     CU(cudaStreamSynchronize(e->hstream));
+    if (g_timeline.path && e->probe_ev[4] && g_timeline.rows.size() < 10 * 4096) {
+        const double out = HostTimeline::now_ms() - g_timeline.cpu0;
+        float t[5];
+        for (int k = 0; k < 5; ++k) CU(cudaEventElapsedTime(&t[k], g_timeline.origin, e->probe_ev[k]));
+        g_timeline.rows.push_back((float)((uintptr_t)e >> 4 & 0xffff));
+        for (int k = 0; k < 5; ++k) g_timeline.rows.push_back(t[k]);
+        for (int k = 0; k < 3; ++k) g_timeline.rows.push_back((float)e->probe_cpu[k]);
+        g_timeline.rows.push_back((float)out);
+    }
     return CF_OK;
 }
 
