@@ -64,6 +64,7 @@ def parse():
     ap.add_argument('--shards', type=int, default=16, help='independent env shards per GPU (L2 eviction; every shard is its own handle)')
     ap.add_argument('--kfuse', type=int, default=32, help='control steps per launch in the fused side measurement')
     ap.add_argument('--e2e-steps', type=int, default=200)
+    ap.add_argument('--e2e-separate', action='store_true', help='e2e: four separate pinned output arrays per buffer set (four downloads per step) instead of one adjacent block')
     ap.add_argument('--e2e-depth', type=int, default=8, help='host-pointer steps in flight (pinned buffer sets; at most one per shard) of the e2e measurement')
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -469,9 +470,21 @@ def main_ours(args):
     D = max(1, min(args.e2e_depth, S))
     sets, ptrs = [], []
     for _ in range(D):
-        bufs = [pinned((n, 4), np.float32), pinned((n, od), np.float32), pinned((n,), np.float32), pinned((n,), np.uint8),
-                pinned((n,), np.float32)]
-        sets.append([b for b, _ in bufs]); ptrs += [q for _, q in bufs]
+        a_buf, a_ptr = pinned((n, 4), np.float32)
+        ptrs.append(a_ptr)
+        if args.e2e_separate or n % 4:
+            bufs = [pinned((n, od), np.float32), pinned((n,), np.float32), pinned((n,), np.uint8), pinned((n,), np.float32)]
+            o_buf, r_buf, d_buf, c_buf = (b for b, _ in bufs); ptrs += [q for _, q in bufs]
+        else:
+            # the four output arrays adjacent in ONE pinned block, in the order the library documents (obs | rew | cost | done):
+            # cf_step_host_async then downloads them with a single copy
+            blk, b_ptr = pinned((n * (4 * od + 9),), np.uint8)
+            ptrs.append(b_ptr)
+            o_buf = blk[:4 * n * od].view(np.float32).reshape(n, od)
+            r_buf = blk[4 * n * od:4 * n * (od + 1)].view(np.float32)
+            c_buf = blk[4 * n * (od + 1):4 * n * (od + 2)].view(np.float32)
+            d_buf = blk[4 * n * (od + 2):]
+        sets.append([a_buf, o_buf, r_buf, d_buf, c_buf])
         sets[-1][0][:] = acts[0].cpu().numpy()
     ke = max(3 * D, args.e2e_steps)                    # its own step count: a region of K = 20 steps would be 7 pipeline fills
 
@@ -496,7 +509,9 @@ def main_ours(args):
         L.cf_host_free(q)
     e2e_h2d, e2e_d2h = n * 16, n * (4 * od + 4 + 1 + 4)
     e2e_api = (f'cf_step_host_async + cf_host_sync (C ABI, pinned host buffers, {D} steps in flight over the shards; '
-               'uploads and downloads inside the timed region)')
+               + ('four output arrays, four downloads per step; ' if (args.e2e_separate or n % 4) else
+                  'obs | rew | cost | done adjacent in one pinned block: one download per step; ')
+               + 'uploads and downloads inside the timed region)')
 
     if rank == 0:
         peak, peak_src = measured_peaks()

@@ -75,6 +75,7 @@ struct cf_env {
     cudaStream_t last_dev_stream = nullptr;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_cost = nullptr, *d_term = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
+    uint8_t* d_out_slab = nullptr;                          // d_obs | d_rew | d_cost | d_done carved from one allocation (ensure_outputs)
     bool tables_borrowed = false;    // tables belong to another handle (cf_share_hj_tables)
     long long launches = 0;
     unsigned long long* trace = nullptr;   // caller-owned device buffer (cf_set_trace_buffer)
@@ -328,6 +329,28 @@ int ensure(T** p, size_t count) {
     return CF_OK;
 }
 
+// Device-side outputs of the host-pointer API, in ONE allocation laid out [obs n x od floats | rew n floats | cost n floats | done n
+// bytes] (n % 4 == 0: every section starts 16-byte aligned): a caller whose host arrays are adjacent in the same order gets them
+// in one download (step_host_enqueue).  Other n: four allocations as before.
+int ensure_outputs(cf_env* e) {
+    if (e->d_obs && e->d_rew && e->d_cost && e->d_done) return CF_OK;
+    const size_t n = e->n, od = e->obs_dim;
+    if (n % 4 == 0 && !e->d_obs && !e->d_rew && !e->d_cost && !e->d_done) {
+        cudaError_t err = cudaMalloc((void**)&e->d_out_slab, n * (od * sizeof(float) + 2 * sizeof(float) + 1));
+        if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc"); return CF_ERR_ALLOC; }
+        e->d_obs = (float*)e->d_out_slab;
+        e->d_rew = e->d_obs + n * od;
+        e->d_cost = e->d_rew + n;
+        e->d_done = (uint8_t*)(e->d_cost + n);
+        return CF_OK;
+    }
+    int rc = ensure(&e->d_obs, n * od);
+    if (rc == CF_OK) rc = ensure(&e->d_rew, n);
+    if (rc == CF_OK) rc = ensure(&e->d_cost, n);
+    if (rc == CF_OK) rc = ensure(&e->d_done, n);
+    return rc;
+}
+
 }  // namespace
 
 extern "C" {
@@ -419,8 +442,9 @@ int cf_destroy(cf_env* e) {
     cudaFree(e->signs_slab); cudaFree((void*)e->value_ptrs_dev); cudaFree(e->thr_dev);
     for (int i = 0; i < 4; ++i) cudaFree(e->inj[i]);
     cudaFree(e->reset_list); cudaFree(e->reset_count); cudaFree(e->S); cudaFree(e->fin_ret); cudaFree(e->fin_len); cudaFree(e->agg); cudaFree(e->rec_dev);
-    cudaFree(e->d_act); cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_term);
-    cudaFree(e->d_done); cudaFree(e->d_trunc); cudaFree(e->d_mask);
+    if (e->d_out_slab) cudaFree(e->d_out_slab);
+    else { cudaFree(e->d_obs); cudaFree(e->d_rew); cudaFree(e->d_cost); cudaFree(e->d_done); }
+    cudaFree(e->d_act); cudaFree(e->d_term); cudaFree(e->d_trunc); cudaFree(e->d_mask);
     for (EventPair& p : e->ev_pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     if (e->order_ev) cudaEventDestroy(e->order_ev);
     if (e->hstream) cudaStreamDestroy(e->hstream);
@@ -502,7 +526,7 @@ int cf_reset_host(cf_env* e, const uint8_t* mask, float* obs) {
     if (!e || !obs) return fail(CF_ERR_INVALID, "cf_reset: null argument%s", "");
     CU(cudaSetDevice(e->device));
     const size_t n = e->n, od = e->obs_dim;
-    int rc = ensure(&e->d_obs, n * od);
+    int rc = ensure_outputs(e);
     if (rc == CF_OK && mask) rc = ensure(&e->d_mask, n);
     if (rc != CF_OK) return rc;
     cudaStream_t st = e->hstream;
@@ -544,10 +568,7 @@ static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew
     CU(cudaSetDevice(e->device));
     const size_t n = e->n, od = e->obs_dim;
     int rc = ensure(&e->d_act, n * 4);
-    if (rc == CF_OK) rc = ensure(&e->d_obs, n * od);
-    if (rc == CF_OK) rc = ensure(&e->d_rew, n);
-    if (rc == CF_OK) rc = ensure(&e->d_done, n);
-    if (rc == CF_OK && cost) rc = ensure(&e->d_cost, n);
+    if (rc == CF_OK) rc = ensure_outputs(e);
     if (rc == CF_OK && term_obs) rc = ensure(&e->d_term, n * od);
     if (rc == CF_OK && truncated) rc = ensure(&e->d_trunc, n);
     if (rc != CF_OK) return rc;
@@ -568,11 +589,20 @@ static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew
                      term_obs ? e->d_term : nullptr, truncated ? e->d_trunc : nullptr, st);
     if (rc != CF_OK) return rc;
     if (tl) CU(cudaEventRecord(e->probe_ev[2], st));
-    CU(cudaMemcpyAsync(obs, e->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
-    if (tl) CU(cudaEventRecord(e->probe_ev[3], st));
-    CU(cudaMemcpyAsync(rew, e->d_rew, n * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(done, e->d_done, n, cudaMemcpyDeviceToHost, st));
-    if (cost) CU(cudaMemcpyAsync(cost, e->d_cost, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    // obs | rew | cost | done adjacent in host memory, in the order of the device slab: one download instead of four (each small copy
+    // costs ~4 us of fixed time on the copy engine that paces this path: profiles/r2_e2e_timeline.md)
+    static const bool no_pack = getenv("CF_HOST_NO_PACK") != nullptr;     // tools/ only: A/B
+    const bool packed = !no_pack && e->d_out_slab && cost && rew == obs + n * od && cost == rew + n && done == (uint8_t*)(cost + n);
+    if (packed) {
+        CU(cudaMemcpyAsync(obs, e->d_obs, n * (od * sizeof(float) + 2 * sizeof(float) + 1), cudaMemcpyDeviceToHost, st));
+        if (tl) CU(cudaEventRecord(e->probe_ev[3], st));
+    } else {
+        CU(cudaMemcpyAsync(obs, e->d_obs, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
+        if (tl) CU(cudaEventRecord(e->probe_ev[3], st));
+        CU(cudaMemcpyAsync(rew, e->d_rew, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(done, e->d_done, n, cudaMemcpyDeviceToHost, st));
+        if (cost) CU(cudaMemcpyAsync(cost, e->d_cost, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    }
     if (term_obs) CU(cudaMemcpyAsync(term_obs, e->d_term, n * od * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (truncated) CU(cudaMemcpyAsync(truncated, e->d_trunc, n, cudaMemcpyDeviceToHost, st));
     if (tl) { CU(cudaEventRecord(e->probe_ev[4], st)); e->probe_cpu[1] = HostTimeline::now_ms() - g_timeline.cpu0; }
@@ -701,7 +731,7 @@ int cf_get_poses_dev(cf_env* e, const int32_t* env_idx_dev, int32_t count, float
 int cf_get_levels(cf_env* e, float* levels_host) {
     if (!e || !levels_host) return fail(CF_ERR_INVALID, "cf_get_levels: null argument%s", "");
     CU(cudaSetDevice(e->device));
-    int rc = ensure(&e->d_rew, (size_t)e->n);
+    int rc = ensure_outputs(e);
     if (rc != CF_OK) return rc;
     CU(cudaDeviceSynchronize());
     launch_levels(e->S, e->n, e->d_rew, 0);

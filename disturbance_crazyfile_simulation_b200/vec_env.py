@@ -350,6 +350,40 @@ class CrazyFlieVecEnv:
     def host_sync(self):
         abi.check(self._L.cf_host_sync(self._h))
 
+    def host_buffers(self, pinned: bool = True):
+        """(act, obs, rew, done, cost) NumPy arrays for :meth:`step_host` / :meth:`step_host_async`, the four outputs ADJACENT in
+        one block in the order the library downloads with a single copy (obs | rew | cost | done, include/cf_abi.h); ``pinned``
+        takes the block from ``cf_host_alloc`` (true asynchronous DMA).  Keep the returned ``owner`` alive (it frees the pinned
+        memory when collected): returns ``(arrays, owner)``."""
+        n, od = self.num_envs, self.obs_dim
+        nbytes = n * (4 * od + 9)
+
+        class _Owner:
+            def __init__(o, L, sizes):
+                o._L, o.ptrs = L, []
+                for sz in sizes:
+                    q = L.cf_host_alloc(sz)
+                    if not q:
+                        raise MemoryError(L.cf_last_error().decode())
+                    o.ptrs.append(q)
+
+            def __del__(o):
+                for q in o.ptrs:
+                    o._L.cf_host_free(q)
+                o.ptrs = []
+
+        if pinned:
+            owner = _Owner(self._L, (16 * n, nbytes))
+            raw = lambda q, sz: np.ctypeslib.as_array((C.c_uint8 * sz).from_address(q))
+            act, blk = raw(owner.ptrs[0], 16 * n).view(np.float32).reshape(n, 4), raw(owner.ptrs[1], nbytes)
+        else:
+            owner, act, blk = None, np.zeros((n, 4), np.float32), np.zeros(nbytes, np.uint8)
+        obs = blk[:4 * n * od].view(np.float32).reshape(n, od)
+        rew = blk[4 * n * od:4 * n * (od + 1)].view(np.float32)
+        cost = blk[4 * n * (od + 1):4 * n * (od + 2)].view(np.float32)
+        done = blk[4 * n * (od + 2):]
+        return (act, obs, rew, done, cost), owner
+
     # ------------------------------------------------------------------ penalty terms (what the reference logs per step)
     def penalty_terms(self, action, physical_done, state: Optional[np.ndarray] = None) -> dict:
         """The terms ``compute_reward`` keeps for logging (hover_free.py:206-235: ``penalty_crash_log``, ``penalty_rpy_log``,

@@ -183,7 +183,11 @@ int cf_step_host(cf_env* env, const float* act, float* obs, float* rew, uint8_t*
 
 /* The same step, not waited for: the copies and the kernel are queued on the handle's private stream and the call
  * returns; the host buffers (pinned: cf_host_alloc) must stay untouched until cf_host_sync(env) returns.  Lets a caller
- * with several handles overlap one handle's download with the next one's upload and kernel. */
+ * with several handles overlap one handle's download with the next one's upload and kernel.
+ * ONE DOWNLOAD PER STEP (both calls): when num_envs is a multiple of 4 and the output arrays are ADJACENT in host memory in the
+ * order obs [n][obs_dim] | rew [n] | cost [n] | done [n] - i.e. rew == obs + n * obs_dim, cost == rew + n, done == (uint8_t*)(cost + n),
+ * one block of n * (4 * obs_dim + 9) bytes - they arrive as a single copy instead of four (each separate copy costs ~4 us of fixed
+ * time on the copy engine that paces this path: 3.4e8 -> 3.6e8 env-steps/s on one B200).  Any other arrangement works as before. */
 int cf_step_host_async(cf_env* env, const float* act, float* obs, float* rew, uint8_t* done,
                        float* cost, float* term_obs, uint8_t* truncated);
 int cf_host_sync(cf_env* env);

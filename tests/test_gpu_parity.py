@@ -473,6 +473,43 @@ def test_host_async_matches_host_sync():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('n', [300, 4096, 301])
+def test_host_step_with_adjacent_output_arrays_is_one_download_with_the_same_bytes(n):
+    """cf_step_host[_async] with obs | rew | cost | done adjacent in one host block (the layout of include/cf_abi.h: a single
+    download per step) against four separate arrays: identical bytes, step after step, resets included.  n = 301 is not a
+    multiple of 4: the library keeps four device buffers and four copies there, the adjacent block must still work."""
+    env_id = 'DroneHoverBulletFreeEnvWithRandomHJAdversary-v0'
+    a, b = make(env_id, num_envs=n, seed=4), make(env_id, num_envs=n, seed=4)
+    od = a.obs_dim
+    oa, ra, da, ca = np.zeros((n, od), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros(n, np.float32)
+    blk = np.full(n * (4 * od + 9) + 64, 0xAB, np.uint8)                   # 64 guard bytes behind the block
+    ob = blk[:4 * n * od].view(np.float32).reshape(n, od)
+    rb = blk[4 * n * od:4 * n * (od + 1)].view(np.float32)
+    cb = blk[4 * n * (od + 1):4 * n * (od + 2)].view(np.float32)
+    db = blk[4 * n * (od + 2):n * (4 * od + 9)]
+    owner = None
+    if n == 4096:                                                           # the wrapper's own pinned, adjacent buffers
+        (act_b, ob, rb, db, cb), owner = b.host_buffers(pinned=True)
+        assert rb.ctypes.data == ob.ctypes.data + 4 * n * od and cb.ctypes.data == rb.ctypes.data + 4 * n and db.ctypes.data == cb.ctypes.data + 4 * n
+    a.reset_host(oa); b.reset_host(ob)
+    assert np.array_equal(oa, ob)
+    rng = np.random.default_rng(0)
+    for t in range(40):
+        act = (0.111 + 0.4 * rng.standard_normal((n, 4))).astype(np.float32)       # wild enough to finish episodes
+        a.step_host(act, oa, ra, da, ca)
+        if owner is not None:
+            act_b[:] = act; act = act_b
+        if t % 2:
+            b.step_host(act, ob, rb, db, cb)
+        else:
+            b.step_host_async(act, ob, rb, db, cb); b.host_sync()
+        assert np.array_equal(oa, ob) and np.array_equal(ra, rb) and np.array_equal(da, db) and np.array_equal(ca, cb), t
+    assert (blk[n * (4 * od + 9):] == 0xAB).all() if owner is None else True     # nothing written behind the block
+    a.close(); b.close()
+    del owner
+
+
+@pytest.mark.gpu
 def test_pd_actions_kernel_and_closed_loop():
     """cf_pd_actions_dev against its formula in NumPy, and closed loop: with the PD law on the noisy observation the
     RandomHJ hover env reaches its 500-step TimeLimit in most episodes (the CPU oracle gives a mean length of ~486)."""
