@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: CF_PROBE_SKIP_SMALL_D2H existed only in the probe build this script measured (profiles/r2_e2e_timeline.md); not in the tree.
 # e2e: how much of a step's 0.21 ms is the fixed cost of the small D2H copies (rew, done, cost)?  Same box, product then probe then product.
 mkdir -p gpurun_out
 for mode in product skip product; do

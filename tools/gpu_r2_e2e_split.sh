@@ -1,4 +1,6 @@
 #!/bin/bash
+# NOTE: CF_HOST_SPLIT / CF_HOST_UPLOAD existed only in the experiment build this script measured (profiles/r2_e2e_timeline.md, last
+# experiment); the switches are not in the tree - kept as the record of what was run.
 # e2e: {single stream, split download stream} x {DMA upload, kernel upload} at depth 3 and 8, one box, two rounds
 mkdir -p gpurun_out; : > gpurun_out/e2e_split.log
 for rep in 1 2; do

@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: the 'skip' leg used CF_PROBE_SKIP_SMALL_D2H, a probe-build switch that is not in the tree; CF_PROBE_E2E_TIMELINE is.
 # e2e timeline (CUDA events per host-pointer step): product, then with the small downloads skipped
 mkdir -p gpurun_out
 for mode in product skip; do

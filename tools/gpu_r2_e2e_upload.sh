@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: CF_HOST_UPLOAD existed only in the experiment build this script measured (profiles/r2_e2e_timeline.md); not in the tree.
 # e2e: action upload by kernel (default now) against the DMA upload, same box; then the host-pointer parity tests
 mkdir -p gpurun_out
 for mode in dma kernel dma kernel; do

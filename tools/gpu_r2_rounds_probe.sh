@@ -1,4 +1,6 @@
 #!/bin/bash
+# NOTE: the variant libraries (csrc/variants/libcf_r7.so, libcf_r4.so) are built ad hoc with build.build(extra_flags=['-DCF_PHILOX_ROUNDS=7'],
+# out=...) and are not kept; results: profiles/r2_kstep_ab.md section 8.
 # timing-only probe (wrong random numbers): how much of a k_step launch is Philox instruction count?  Product library first, then
 # builds with 7 and 4 Philox rounds (tools only; -DCF_PHILOX_ROUNDS), same bench command, one box.
 mkdir -p gpurun_out
