@@ -592,7 +592,9 @@ static int step_host_enqueue(cf_env* e, const float* act, float* obs, float* rew
     // obs | rew | cost | done adjacent in host memory, in the order of the device slab: one download instead of four (each small copy
     // costs ~4 us of fixed time on the copy engine that paces this path: profiles/r2_e2e_timeline.md)
     static const bool no_pack = getenv("CF_HOST_NO_PACK") != nullptr;     // tools/ only: A/B
-    const bool packed = !no_pack && e->d_out_slab && cost && rew == obs + n * od && cost == rew + n && done == (uint8_t*)(cost + n);
+    const uintptr_t ho = (uintptr_t)obs, hr = (uintptr_t)rew, hc = (uintptr_t)cost, hd = (uintptr_t)done;   // addresses: the arrays may be unrelated objects
+    const bool packed = !no_pack && e->d_out_slab && cost && hr == ho + n * od * sizeof(float) && hc == hr + n * sizeof(float) &&
+                        hd == hc + n * sizeof(float);
     if (packed) {
         CU(cudaMemcpyAsync(obs, e->d_obs, n * (od * sizeof(float) + 2 * sizeof(float) + 1), cudaMemcpyDeviceToHost, st));
         if (tl) CU(cudaEventRecord(e->probe_ev[3], st));
